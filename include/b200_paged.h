@@ -1,0 +1,203 @@
+/*
+ * b200_paged.h — C ABI of libb200_paged.so: the B200-native (sm_100a) decode hot path of
+ * light-vllm: paged attention over the block-table KV cache plus the cache-write /
+ * cache-management ops that feed it.
+ *
+ * This is the drop-in boundary.  Every entry point takes plain pointers, sizes and strides
+ * (no torch types) and launches on the caller's stream without synchronising.  Each function
+ * names the reference interface it replaces (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - return value: 0 on success, a B200_ERR_* code otherwise; b200_last_error() returns a
+ *     thread-local human-readable message for the last failing call on this thread
+ *     (the reference raises via TORCH_CHECK -> RuntimeError; the torch binding converts
+ *     non-zero codes to exactly that).
+ *   - `device`: CUDA ordinal that owns the device pointers; the call makes it current for the
+ *     duration of the call (reference: at::cuda::OptionalCUDAGuard, attention_kernels.cu:736).
+ *   - `stream`: a cudaStream_t (reference: at::cuda::getCurrentCUDAStream(), :737).
+ *   - strides are in ELEMENTS of the tensor they index and are 64-bit (the reference uses
+ *     int, attention_kernels.cu:705-707; pools above 2^31 elements need 64 bits).
+ *   - there is no CPU implementation behind any of these symbols: without a CUDA device they
+ *     fail with B200_ERR_CUDA.
+ */
+#ifndef B200_PAGED_H_
+#define B200_PAGED_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_PAGED_ABI_VERSION 1
+
+typedef struct CUstream_st* b200_stream_t; /* == cudaStream_t */
+
+/* Query / activation dtype (reference: query.dtype(), quant_utils.cuh:532-569). */
+enum { B200_DT_F32 = 0, B200_DT_F16 = 1, B200_DT_BF16 = 2 };
+
+/* KV-cache storage format (reference: Fp8KVCacheDataType, csrc/attention/dtype_fp8.cuh:14-18). */
+enum { B200_KV_AUTO = 0, B200_KV_FP8_E4M3 = 1, B200_KV_FP8_E5M2 = 2 };
+
+enum {
+  B200_OK = 0,
+  B200_ERR_INVALID = 1,     /* bad argument / inconsistent shapes                         */
+  B200_ERR_UNSUPPORTED = 2, /* head size / block size / dtype combo not instantiated      */
+  B200_ERR_CUDA = 3         /* CUDA runtime error (message carries cudaGetErrorString)    */
+};
+
+/* Blocksparse tail of the paged_attention schema (csrc/torch_bindings.cpp:31-34;
+ * semantics attention_kernels.cu:209-256,387-393).  Pass NULL or vert_stride <= 1 for dense. */
+typedef struct {
+  int32_t tp_rank;
+  int32_t local_blocks;
+  int32_t vert_stride;
+  int32_t block_size;
+  int32_t head_sliding_step;
+} b200_blocksparse_t;
+
+/* Thread-local message of the last failing call on this thread ("" if none). */
+const char* b200_last_error(void);
+
+int b200_abi_version(void);
+
+/* Maps the reference's kv_cache_dtype strings "auto" | "fp8" | "fp8_e4m3" | "fp8_e5m2"
+ * (quant_utils.cuh:533,544,555) to B200_KV_*; returns -1 for anything else. */
+int b200_parse_kv_cache_dtype(const char* s);
+
+/*
+ * paged_attention_v1 — replaces torch.ops._C.paged_attention_v1
+ *   (csrc/torch_bindings.cpp:24-35, csrc/attention/attention_kernels.cu:808-829, :690-770).
+ *
+ *   out          [num_seqs, num_heads, head_size]            T, dense
+ *   query        [num_seqs, num_heads, head_size]            T, row stride q_stride
+ *   key_cache    [num_blocks, num_kv_heads, head_size/x, block_size, x]   x = 16 / sizeof(cache elem)
+ *   value_cache  [num_blocks, num_kv_heads, head_size, block_size]
+ *                cache elem = T for B200_KV_AUTO, uint8 (fp8) otherwise;
+ *                kv_block_stride / kv_head_stride index dim 0 / dim 1 of BOTH caches
+ *   block_tables [num_seqs, max_num_blocks_per_seq] int32;  seq_lens [num_seqs] int32
+ *   alibi_slopes [num_heads] float32 or NULL
+ */
+int b200_paged_attention_v1(void* out, const void* query, const void* key_cache,
+                            const void* value_cache, const int32_t* block_tables,
+                            const int32_t* seq_lens, const float* alibi_slopes, int num_seqs,
+                            int num_heads, int num_kv_heads, int head_size, int block_size,
+                            int max_seq_len, int max_num_blocks_per_seq, int64_t q_stride,
+                            int64_t kv_block_stride, int64_t kv_head_stride, float scale,
+                            float k_scale, float v_scale, int q_dtype, int kv_dtype,
+                            const b200_blocksparse_t* blocksparse, int device,
+                            b200_stream_t stream);
+
+/*
+ * paged_attention_v2 — replaces torch.ops._C.paged_attention_v2
+ *   (csrc/torch_bindings.cpp:37-48, attention_kernels.cu:973-997, :848-934, reduce :565-669).
+ *   Split-context: 512-token partitions write
+ *     tmp_out    [num_seqs, num_heads, max_num_partitions, head_size]  T
+ *     max_logits [num_seqs, num_heads, max_num_partitions]  float32
+ *     exp_sums   [num_seqs, num_heads, max_num_partitions]  float32
+ *   (caller-owned scratch, paged_attn.py:156-166) and a second kernel merges them into `out`.
+ *   max_num_partitions must be >= ceil(max_seq_len / 512).
+ */
+int b200_paged_attention_v2(void* out, float* exp_sums, float* max_logits, void* tmp_out,
+                            const void* query, const void* key_cache, const void* value_cache,
+                            const int32_t* block_tables, const int32_t* seq_lens,
+                            const float* alibi_slopes, int num_seqs, int num_heads,
+                            int num_kv_heads, int head_size, int block_size, int max_seq_len,
+                            int max_num_blocks_per_seq, int max_num_partitions, int64_t q_stride,
+                            int64_t kv_block_stride, int64_t kv_head_stride, float scale,
+                            float k_scale, float v_scale, int q_dtype, int kv_dtype,
+                            const b200_blocksparse_t* blocksparse, int device,
+                            b200_stream_t stream);
+
+/*
+ * reshape_and_cache — replaces torch.ops._C_cache_ops.reshape_and_cache
+ *   (csrc/torch_bindings.cpp:241-247, csrc/cache_kernels.cu:263-289, kernel :152-204).
+ *   key/value [num_tokens, num_heads, head_size] T with token strides key_stride/value_stride;
+ *   caches dense in the paged layout above; slot_mapping [num_tokens] int64, slot < 0 = skip.
+ *   kv_dtype != AUTO: stored value = fp8(float(x) / scale), saturating (quant_utils.cuh:458-489).
+ */
+int b200_reshape_and_cache(const void* key, const void* value, void* key_cache, void* value_cache,
+                           const int64_t* slot_mapping, int num_tokens, int num_heads,
+                           int head_size, int block_size, int x, int64_t key_stride,
+                           int64_t value_stride, float k_scale, float v_scale, int src_dtype,
+                           int kv_dtype, int device, b200_stream_t stream);
+
+/*
+ * reshape_and_cache_flash — replaces torch.ops._C_cache_ops.reshape_and_cache_flash
+ *   (csrc/torch_bindings.cpp:250-258, csrc/cache_kernels.cu:304-330, kernel :206-247).
+ *   caches [num_blocks, block_size, num_heads, head_size] with dim-0 stride block_stride.
+ */
+int b200_reshape_and_cache_flash(const void* key, const void* value, void* key_cache,
+                                 void* value_cache, const int64_t* slot_mapping, int num_tokens,
+                                 int num_heads, int head_size, int block_size,
+                                 int64_t block_stride, int64_t key_stride, int64_t value_stride,
+                                 float k_scale, float v_scale, int src_dtype, int kv_dtype,
+                                 int device, b200_stream_t stream);
+
+/*
+ * copy_blocks — replaces torch.ops._C_cache_ops.copy_blocks
+ *   (csrc/torch_bindings.cpp:235-238, csrc/cache_kernels.cu:101-148, kernel :68-94).
+ *   key_cache_ptrs/value_cache_ptrs: HOST arrays of num_layers device base pointers;
+ *   block_mapping: [num_pairs, 2] int64 (src, dst), readable from the device (device memory or
+ *   pinned host memory — light-vllm passes a pinned CPU tensor, model_input_builder.py:93-96);
+ *   block_bytes = bytes of one block of one layer's K (== V) cache.  No host<->device sync.
+ */
+int b200_copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_ptrs, int num_layers,
+                     const int64_t* block_mapping, int num_pairs, int64_t block_bytes, int device,
+                     b200_stream_t stream);
+
+/*
+ * swap_blocks — replaces torch.ops._C_cache_ops.swap_blocks
+ *   (csrc/torch_bindings.cpp:230-232, csrc/cache_kernels.cu:24-63).
+ *   block_mapping_host: HOST [num_pairs, 2] int64 (src block, dst block) — the reference requires a
+ *   CPU tensor (:44).  src_device / dst_device: CUDA ordinal, or -1 for host memory.
+ *   Host<->device pairs over pinned host memory run as one gather/scatter kernel per 224 pairs;
+ *   pageable host memory falls back to run-merged cudaMemcpyAsync.  Stream-ordered, no sync.
+ */
+int b200_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host, int num_pairs,
+                     int64_t block_bytes, int src_device, int dst_device, b200_stream_t stream);
+
+/*
+ * convert_fp8 — replaces torch.ops._C_cache_ops.convert_fp8
+ *   (csrc/torch_bindings.cpp:261-264, csrc/cache_kernels.cu:355-405, kernel :334-345).
+ *   Direction from dtypes: exactly one of src/dst is fp8 (uint8); `wide_dtype` is the B200_DT_* of
+ *   the other side.  to_fp8 != 0: dst = fp8(float(src)/scale); else dst = T(float(half(src))*scale).
+ */
+int b200_convert_fp8(void* dst, const void* src, int64_t numel, float scale, int wide_dtype,
+                     int kv_dtype, int to_fp8, int device, b200_stream_t stream);
+
+/*
+ * get_device_attribute / get_max_shared_memory_per_block_device_attribute — replace
+ *   torch.ops._C_cuda_utils.* (csrc/torch_bindings.cpp:271-279, csrc/cuda_utils_kernels.cu:8-29).
+ *   Return the attribute value, or -1 on error.
+ */
+int64_t b200_get_device_attribute(int64_t attribute, int64_t device_id);
+int64_t b200_get_max_shared_memory_per_block_device_attribute(int64_t device_id);
+
+/* Introspection used by bench.py / tests: launch geometry the library would pick. */
+typedef struct {
+  int32_t cluster_size;   /* v1: CTAs per (seq, kv-head) cooperating through DSMEM */
+  int32_t num_warps;      /* warps per CTA                                        */
+  int32_t num_stages;     /* K+V page pairs in flight per warp                    */
+  int32_t smem_bytes;     /* dynamic shared memory per CTA                        */
+  int32_t ctas_per_sm;    /* occupancy reported by the runtime                    */
+  int32_t grid_x, grid_y, grid_z;
+} b200_attn_plan_t;
+int b200_paged_attention_plan(int version, int num_seqs, int num_heads, int num_kv_heads,
+                              int head_size, int block_size, int max_seq_len, int q_dtype,
+                              int kv_dtype, int device, b200_attn_plan_t* plan);
+
+/* Tuning knobs (benchmarking / autotuning; 0 restores the library default).
+ *   b200_set_attn_tuning: warps per CTA, ring stages per warp, v1 cluster size.
+ *     Also settable through env B200_ATTN_WARPS / B200_ATTN_STAGES / B200_ATTN_CLUSTER.
+ *   b200_set_swap_mode: 0 auto, 1 force run-merged cudaMemcpyAsync, 2 force the copy kernel. */
+void b200_set_attn_tuning(int warps, int stages, int cluster);
+void b200_set_swap_mode(int mode);
+
+/* Number of kernels this library has launched from the calling process (for gpu_launches). */
+int64_t b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_PAGED_H_ */

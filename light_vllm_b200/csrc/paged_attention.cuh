@@ -1,0 +1,310 @@
+// Paged-attention decode kernel for sm_100a — replaces the reference's
+// paged_attention_kernel / _v1_kernel / _v2_kernel (csrc/attention/attention_kernels.cu:86-562).
+//
+// Design (B200-first, not a translation of the reference's SIMT kernel):
+//   * one CTA per (sequence, KV head, context split); ALL q-heads of the GQA group are computed
+//     from ONE read of each KV page (the reference launches one CTA per q-head and re-reads the
+//     page H/KH times, attention_kernels.cu:150-153,734).
+//   * every warp streams its own interleaved subset of the split's pages through a private
+//     multi-stage shared-memory ring.  A K page and a V page are each one contiguous
+//     head_size*block_size run in the reference layout, so each is fetched with ONE
+//     cp.async.bulk (TMA engine, SASS UBLKCP) that signals an mbarrier with complete_tx.
+//     No register staging, no per-thread address math, no CTA-wide barrier in the main loop.
+//   * QK^T and PV run on tensor cores (mma.sync m16n8k16, fp32 accumulate) with the q-head group
+//     as the (padded) M dimension: A = Q[16 x D] from registers, B = K page via ldmatrix straight
+//     from the reference layout [D/8][BS][8]; P stays in registers and becomes the A operand of
+//     PV, B = V page [D][BS] via ldmatrix.  At HBM speed the CUDA-core formulation would need
+//     35-100+% of the FP32 issue rate; this needs ~32 HMMA + ~16 LDSM per page.
+//   * streaming (online) softmax per warp in the exp2 domain; warps merge through shared memory;
+//     context splits merge either through distributed shared memory inside a thread-block
+//     cluster (v1: no scratch in the op schema) or through the caller's scratch + the reduce
+//     kernel (v2, 512-token partitions as in attention_kernels.cu:850,888-897).
+#pragma once
+
+#include "common.cuh"
+
+namespace b200 {
+
+struct AttnParams {
+  void* out;               // v1: [B, H, D] T
+  float* exp_sums;         // v2: [B, H, P]
+  float* max_logits;       // v2: [B, H, P]
+  void* tmp_out;           // v2: [B, H, P, D] T
+  const void* q;           // [B, H, D] T, row stride q_stride
+  const void* k_cache;     // [NB, KH, D/x, BS, x]
+  const void* v_cache;     // [NB, KH, D, BS]
+  const int32_t* block_tables;  // [B, max_blocks_per_seq]
+  const int32_t* seq_lens;      // [B]
+  const float* alibi_slopes;    // [H] or null
+  int num_heads, num_kv_heads, group;  // group = H / KH
+  int gchunks;                  // ceil(group / GROWS)
+  int max_blocks_per_seq;
+  int max_num_partitions;       // v2 only
+  int partition_pages;          // v2: pages per 512-token partition; v1: 0
+  int num_stages;               // ring depth per warp
+  int64_t q_stride, kv_block_stride, kv_head_stride;  // elements
+  float scale_log2;             // scale * log2(e) (* k_scale for fp8 caches)
+  float out_scale;              // v_scale for fp8 caches, else 1
+  int bs_enabled, bs_tp_rank, bs_local_blocks, bs_vert_stride, bs_block_size,
+      bs_head_sliding_step;
+};
+
+// Dispatch table entry exported by each instantiation TU (paged_attention_inst_*.cu).
+using AttnLaunchFn = int (*)(const AttnParams&, dim3, int, int, int, int, cudaStream_t);
+using AttnSmemFn = size_t (*)(int, int);
+using AttnOccFn = int (*)(int, int);
+struct AttnEntry {
+  AttnLaunchFn launch;     // (params, grid, cluster, nwarps, nstages, device, stream)
+  AttnSmemFn smem;         // (nwarps, nstages) -> dynamic shared memory bytes
+  AttnOccFn occupancy;     // (nwarps, nstages) -> resident CTAs per SM
+};
+
+constexpr float kNegInf = -__builtin_huge_valf();
+constexpr int kMergePad = 8;  // floats of padding per merged row (bank spread)
+
+template <int KV>
+struct KvTraits {
+  static constexpr int ES = (KV == B200_KV_AUTO) ? 2 : 1;  // bytes per cache element
+};
+
+// MMA element type: the cache's own 16-bit type for "auto"; fp16 for fp8 caches (e4m3/e5m2 -> f16
+// is exact, and q is converted to f16 once per CTA).
+template <typename T, int KV>
+struct MmaType {
+  using type = T;
+};
+template <typename T>
+struct MmaType<T, B200_KV_FP8_E4M3> {
+  using type = __half;
+};
+template <typename T>
+struct MmaType<T, B200_KV_FP8_E5M2> {
+  using type = __half;
+};
+
+template <int KV>
+__device__ __forceinline__ uint32_t fp8x2_to_f16x2(uint16_t v) {
+  constexpr __nv_fp8_interpretation_t kind = (KV == B200_KV_FP8_E5M2) ? __NV_E5M2 : __NV_E4M3;
+  __half2_raw h = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)v, kind);
+  return (uint32_t)h.x | ((uint32_t)h.y << 16);
+}
+
+// One KV page (BS tokens) against the warp's q-group: S = QK^T, online softmax, O += P V.
+template <typename T, int D, int BS, int KV, int GROWS, bool TAIL>
+__device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
+                                             const uint32_t (&qa)[(D + 15) / 16][GROWS / 4],
+                                             float (&o)[D / 8][GROWS / 4], float (&m)[GROWS / 8],
+                                             float (&l)[GROWS / 8], int lane, int valid,
+                                             float scale_log2, const float (&slope)[GROWS / 8],
+                                             float tok_rel0,  // (first token of page) - seq_len + 1
+                                             const bool (&row_on)[GROWS / 8]) {
+  using MT = typename MmaType<T, KV>::type;
+  constexpr int ES = KvTraits<KV>::ES;
+  constexpr int KS = (D + 15) / 16;  // k-steps over head dim
+  constexpr int NT = BS / 8;         // 8-token n-tiles in a page
+  constexpr int RS = GROWS / 8;      // row sets (rows g, g+8)
+  constexpr int NDT = D / 8;         // 8-wide d tiles of the output
+  const int q4 = lane & 3;
+  const int mi = lane >> 3, r8 = lane & 7;
+
+  // ---------------- S = Q K^T ----------------
+  float s[NT][4];
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+
+  if constexpr (KV == B200_KV_AUTO) {
+    // K page layout [D/8][BS][8] (16-byte rows).  ldmatrix row addresses for this lane.
+    if constexpr (BS >= 16) {
+      const uint32_t base = k_smem + (uint32_t)((mi & 1) * BS * 16 + ((mi >> 1) * 8 + r8) * 16);
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+        for (int th = 0; th < NT / 2; ++th) {  // 16 tokens per ldmatrix.x4
+          uint32_t b00, b01, b10, b11;
+          ldsm_x4(base + (uint32_t)(ks * 2 * BS * 16 + th * 16 * 16), b00, b01, b10, b11);
+          if (2 * ks + 1 >= NDT) b01 = b11 = 0u;  // odd chunk count (head 120): no such chunk
+          const uint32_t a1 = (RS == 2) ? qa[ks][2] : 0u, a3 = (RS == 2) ? qa[ks][3] : 0u;
+          MmaOp<MT>::run(s[2 * th], qa[ks][0], a1, qa[ks][1], a3, b00, b01);
+          MmaOp<MT>::run(s[2 * th + 1], qa[ks][0], a1, qa[ks][1], a3, b10, b11);
+        }
+      }
+    } else {  // BS == 8: one n-tile, ldmatrix.x2 (lanes 0-15 supply addresses)
+      const uint32_t base = k_smem + (uint32_t)((mi & 1) * BS * 16 + r8 * 16);
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        uint32_t b0, b1;
+        ldsm_x2(base + (uint32_t)(ks * 2 * BS * 16), b0, b1);
+        if (2 * ks + 1 >= NDT) b1 = 0u;
+        const uint32_t a1 = (RS == 2) ? qa[ks][2] : 0u, a3 = (RS == 2) ? qa[ks][3] : 0u;
+        MmaOp<MT>::run(s[0], qa[ks][0], a1, qa[ks][1], a3, b0, b1);
+      }
+    }
+  } else {
+    // fp8 K page layout [D/16][BS][16].  Lane (n = lane/4, q4) reads 4 bytes: d = 16ks + 4*q4 + 0..3
+    // of token 8nt + n; (d0,d1) -> b0, (d2,d3) -> b1.  Q fragments are loaded with the matching
+    // d permutation (see load_q).
+    const uint32_t base = k_smem + (uint32_t)((lane >> 2) * 16 + q4 * 4);
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        uint32_t w;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(base + (uint32_t)(ks * BS * 16 + nt * 8 * 16)));
+        const uint32_t b0 = fp8x2_to_f16x2<KV>((uint16_t)(w & 0xffffu));
+        const uint32_t b1 = fp8x2_to_f16x2<KV>((uint16_t)(w >> 16));
+        const uint32_t a1 = (RS == 2) ? qa[ks][2] : 0u, a3 = (RS == 2) ? qa[ks][3] : 0u;
+        MmaOp<MT>::run(s[nt], qa[ks][0], a1, qa[ks][1], a3, b0, b1);
+      }
+    }
+  }
+
+  // ---------------- online softmax (exp2 domain) ----------------
+  float alpha[RS];
+  bool changed = false;
+#pragma unroll
+  for (int rs = 0; rs < RS; ++rs) {
+    float mx = kNegInf;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int t = nt * 8 + q4 * 2 + e;  // token within page
+        float x = s[nt][2 * rs + e] * scale_log2 + slope[rs] * (tok_rel0 + (float)t);
+        if (TAIL && t >= valid) x = kNegInf;
+        if (!row_on[rs]) x = kNegInf;
+        s[nt][2 * rs + e] = x;
+        mx = fmaxf(mx, x);
+      }
+    }
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+    const float m_new = fmaxf(m[rs], mx);
+    const float m_safe = (m_new == kNegInf) ? 0.f : m_new;
+    alpha[rs] = fast_exp2(m[rs] - m_safe);
+    changed |= (m_new != m[rs]);
+    m[rs] = m_new;
+    float sum = 0.f;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const float pv = fast_exp2(s[nt][2 * rs + e] - m_safe);
+        s[nt][2 * rs + e] = pv;
+        sum += pv;
+      }
+    }
+    l[rs] = l[rs] * alpha[rs] + sum;
+  }
+  if (__any_sync(0xffffffffu, changed)) {  // warp-uniform: the running max rarely moves
+#pragma unroll
+    for (int j = 0; j < NDT; ++j) {
+#pragma unroll
+      for (int rs = 0; rs < RS; ++rs) {
+        o[j][2 * rs] *= alpha[rs];
+        o[j][2 * rs + 1] *= alpha[rs];
+      }
+    }
+  }
+
+  // ---------------- O += P V ----------------
+  // tail masks: V columns past the sequence end may hold NaN; 0 * NaN must not reach the MMA.
+  uint32_t vmask[BS >= 16 ? BS / 8 : 1];
+  if constexpr (TAIL) {
+#pragma unroll
+    for (int h = 0; h < (BS >= 16 ? BS / 8 : 1); ++h) {
+      const int t0 = h * 8 + q4 * 2;
+      vmask[h] = (t0 < valid ? 0x0000ffffu : 0u) | (t0 + 1 < valid ? 0xffff0000u : 0u);
+    }
+  }
+  constexpr int KSV = (BS >= 16) ? BS / 16 : 1;  // k-steps over tokens
+#pragma unroll
+  for (int kk = 0; kk < KSV; ++kk) {
+    uint32_t pa0, pa1, pa2, pa3;
+    if constexpr (BS >= 16) {
+      pa0 = MmaOp<MT>::pack(s[2 * kk][0], s[2 * kk][1]);
+      pa2 = MmaOp<MT>::pack(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+      pa1 = (RS == 2) ? MmaOp<MT>::pack(s[2 * kk][2], s[2 * kk][3]) : 0u;
+      pa3 = (RS == 2) ? MmaOp<MT>::pack(s[2 * kk + 1][2], s[2 * kk + 1][3]) : 0u;
+    } else {
+      pa0 = MmaOp<MT>::pack(s[0][0], s[0][1]);
+      pa1 = (RS == 2) ? MmaOp<MT>::pack(s[0][2], s[0][3]) : 0u;
+      pa2 = pa3 = 0u;
+    }
+    if constexpr (KV == B200_KV_AUTO) {
+      if constexpr (BS >= 16) {
+        // V page [D][BS]: 8x8 matrices = 8 d-rows x 8 tokens (16 B); x4 = 2 d-tiles x 2 token halves
+        const uint32_t base = v_smem + (uint32_t)((((mi >> 1) * 8 + r8) * BS * 2) + (mi & 1) * 16 +
+                                                  kk * 32);
+#pragma unroll
+        for (int jj = 0; jj < (NDT + 1) / 2; ++jj) {
+          uint32_t b00, b01, b10, b11;
+          ldsm_x4(base + (uint32_t)(jj * 16 * BS * 2), b00, b01, b10, b11);
+          if constexpr (TAIL) {
+            b00 &= vmask[2 * kk]; b10 &= vmask[2 * kk];
+            b01 &= vmask[2 * kk + 1]; b11 &= vmask[2 * kk + 1];
+          }
+          {
+            float acc[4] = {o[2 * jj][0], o[2 * jj][1], RS == 2 ? o[2 * jj][2 * (RS - 1)] : 0.f,
+                            RS == 2 ? o[2 * jj][2 * (RS - 1) + 1] : 0.f};
+            MmaOp<MT>::run(acc, pa0, pa1, pa2, pa3, b00, b01);
+            o[2 * jj][0] = acc[0]; o[2 * jj][1] = acc[1];
+            if constexpr (RS == 2) { o[2 * jj][2] = acc[2]; o[2 * jj][3] = acc[3]; }
+          }
+          if (2 * jj + 1 < NDT) {
+            float acc[4] = {o[2 * jj + 1][0], o[2 * jj + 1][1],
+                            RS == 2 ? o[2 * jj + 1][2 * (RS - 1)] : 0.f,
+                            RS == 2 ? o[2 * jj + 1][2 * (RS - 1) + 1] : 0.f};
+            MmaOp<MT>::run(acc, pa0, pa1, pa2, pa3, b10, b11);
+            o[2 * jj + 1][0] = acc[0]; o[2 * jj + 1][1] = acc[1];
+            if constexpr (RS == 2) { o[2 * jj + 1][2] = acc[2]; o[2 * jj + 1][3] = acc[3]; }
+          }
+        }
+      } else {  // BS == 8: rows are 16 B; x4 = 4 d-tiles, tokens 8..15 of the k-step are zero
+        const uint32_t base = v_smem + (uint32_t)((mi * 8 + r8) * 16);
+#pragma unroll
+        for (int jj = 0; jj < (NDT + 3) / 4; ++jj) {
+          uint32_t b[4];
+          ldsm_x4(base + (uint32_t)(jj * 32 * 16), b[0], b[1], b[2], b[3]);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (4 * jj + u < NDT) {
+              uint32_t bb = b[u];
+              if constexpr (TAIL) bb &= vmask[0];
+              float acc[4] = {o[4 * jj + u][0], o[4 * jj + u][1],
+                              RS == 2 ? o[4 * jj + u][2 * (RS - 1)] : 0.f,
+                              RS == 2 ? o[4 * jj + u][2 * (RS - 1) + 1] : 0.f};
+              MmaOp<MT>::run(acc, pa0, pa1, pa2, pa3, bb, 0u);
+              o[4 * jj + u][0] = acc[0]; o[4 * jj + u][1] = acc[1];
+              if constexpr (RS == 2) { o[4 * jj + u][2] = acc[2]; o[4 * jj + u][3] = acc[3]; }
+            }
+          }
+        }
+      }
+    } else {
+      // fp8 V page [D][BS] bytes.  Lane (n = lane/4 -> d = 8j + n, q4) needs tokens (2q4, 2q4+1) and
+      // (8 + 2q4, 9 + 2q4) of the k-step: two 16-bit shared loads.
+      const uint32_t base = v_smem + (uint32_t)((lane >> 2) * BS + q4 * 2 + kk * 16);
+#pragma unroll
+      for (int j = 0; j < NDT; ++j) {
+        uint16_t w0, w1 = 0;
+        asm volatile("ld.shared.u16 %0, [%1];" : "=h"(w0) : "r"(base + (uint32_t)(j * 8 * BS)));
+        if constexpr (BS >= 16)
+          asm volatile("ld.shared.u16 %0, [%1];" : "=h"(w1) : "r"(base + (uint32_t)(j * 8 * BS + 8)));
+        uint32_t b0 = fp8x2_to_f16x2<KV>(w0);
+        uint32_t b1 = (BS >= 16) ? fp8x2_to_f16x2<KV>(w1) : 0u;
+        if constexpr (TAIL) {
+          b0 &= vmask[BS >= 16 ? 2 * kk : 0];
+          if constexpr (BS >= 16) b1 &= vmask[2 * kk + 1];
+        }
+        float acc[4] = {o[j][0], o[j][1], RS == 2 ? o[j][2 * (RS - 1)] : 0.f,
+                        RS == 2 ? o[j][2 * (RS - 1) + 1] : 0.f};
+        MmaOp<MT>::run(acc, pa0, pa1, pa2, pa3, b0, b1);
+        o[j][0] = acc[0]; o[j][1] = acc[1];
+        if constexpr (RS == 2) { o[j][2] = acc[2]; o[j][3] = acc[3]; }
+      }
+    }
+  }
+  (void)ES;
+}
+
+}  // namespace b200

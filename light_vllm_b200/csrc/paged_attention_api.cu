@@ -1,0 +1,352 @@
+// C entry points for paged attention: argument validation, launch planning, dispatch to the
+// instantiated kernels, and the v2 partition-merge kernel
+// (replaces attention_kernels.cu:565-669, 690-770, 808-829, 848-934, 973-997).
+#include "paged_attention.cuh"
+
+#include <atomic>
+#include <cstdlib>
+#include <cstring>
+
+namespace b200 {
+
+AttnEntry attn_lookup_f16_auto(int, int, int);
+AttnEntry attn_lookup_f16_e4m3(int, int, int);
+AttnEntry attn_lookup_f16_e5m2(int, int, int);
+AttnEntry attn_lookup_bf16_auto(int, int, int);
+AttnEntry attn_lookup_bf16_e4m3(int, int, int);
+AttnEntry attn_lookup_bf16_e5m2(int, int, int);
+
+constexpr int kPartitionSize = 512;  // fixed by the op contract (paged_attn.py:14)
+
+// ---------------------------------------------------------------------------------------
+// v2 merge: out = sum_j tmp_out_j * exp_sum_j * e^(m_j - m) / (sum_j exp_sum_j e^(m_j - m) + 1e-6)
+// One warp per (seq, head); 4 (seq, head) pairs per CTA.  (Reference: one 128-thread CTA per pair.)
+// ---------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(128)
+paged_attention_v2_reduce_kernel(T* __restrict__ out, const float* __restrict__ exp_sums,
+                                 const float* __restrict__ max_logits,
+                                 const T* __restrict__ tmp_out, const int32_t* __restrict__ seq_lens,
+                                 int num_heads, int head_size, int max_num_partitions,
+                                 int64_t total_pairs) {
+  const int lane = threadIdx.x & 31;
+  const int64_t pair = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (pair >= total_pairs) return;
+  const int seq = (int)(pair / num_heads);
+  const int seq_len = seq_lens[seq];
+  const int np = (seq_len + kPartitionSize - 1) / kPartitionSize;
+  T* o = out + pair * head_size;
+  const T* t = tmp_out + pair * max_num_partitions * head_size;
+  if (np <= 1) {
+    // np == 1: plain copy (attention_kernels.cu:582-594).  np == 0 (empty sequence): the
+    // partition kernel wrote nothing; define the output as zeros.
+    for (int d = lane; d < head_size; d += 32) o[d] = np == 1 ? t[d] : from_f32<T>(0.f);
+    return;
+  }
+  const float* ml = max_logits + pair * max_num_partitions;
+  const float* es = exp_sums + pair * max_num_partitions;
+  float mx = -__builtin_huge_valf();
+  for (int j = lane; j < np; j += 32) mx = fmaxf(mx, ml[j]);
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+  float sum = 0.f;
+  for (int j = lane; j < np; j += 32) sum += es[j] * expf(ml[j] - mx);
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
+  const float inv = __fdividef(1.f, sum + 1e-6f);
+  for (int d = lane; d < head_size; d += 32) {
+    float acc = 0.f;
+    for (int j = 0; j < np; ++j)
+      acc += to_f32<T>(t[(int64_t)j * head_size + d]) * (es[j] * expf(ml[j] - mx)) * inv;
+    o[d] = from_f32<T>(acc);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// launch planning
+// ---------------------------------------------------------------------------------------
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+// Tuning knobs: env B200_ATTN_WARPS / B200_ATTN_STAGES / B200_ATTN_CLUSTER at first use, or
+// b200_set_attn_tuning() at run time (0 = library default).
+struct Knobs {
+  std::atomic<int> warps, stages, cluster;
+  Knobs()
+      : warps(env_int("B200_ATTN_WARPS", 0)),
+        stages(env_int("B200_ATTN_STAGES", 0)),
+        cluster(env_int("B200_ATTN_CLUSTER", 0)) {}
+};
+static Knobs& knobs() {
+  static Knobs k;
+  return k;
+}
+
+struct Plan {
+  AttnEntry entry;
+  int grows, gchunks, nwarps, nstages, cluster, ctas_per_sm, num_sms;
+  size_t smem;
+};
+
+static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num_kv_heads,
+                     int head_size, int block_size, int max_seq_len, int q_dtype, int kv_dtype,
+                     int device) {
+  B200_CHECK_ARG(num_kv_heads > 0 && num_heads > 0 && num_heads % num_kv_heads == 0,
+                 "num_heads (%d) must be a positive multiple of num_kv_heads (%d)", num_heads,
+                 num_kv_heads);
+  const int group = num_heads / num_kv_heads;
+  pl.grows = (group > 8 && head_size <= 128) ? 16 : 8;
+  pl.gchunks = (group + pl.grows - 1) / pl.grows;
+  AttnEntry e{nullptr, nullptr, nullptr};
+  if (q_dtype == B200_DT_F16) {
+    e = kv_dtype == B200_KV_AUTO       ? attn_lookup_f16_auto(head_size, block_size, pl.grows)
+        : kv_dtype == B200_KV_FP8_E4M3 ? attn_lookup_f16_e4m3(head_size, block_size, pl.grows)
+        : kv_dtype == B200_KV_FP8_E5M2 ? attn_lookup_f16_e5m2(head_size, block_size, pl.grows)
+                                       : e;
+  } else if (q_dtype == B200_DT_BF16) {
+    e = kv_dtype == B200_KV_AUTO       ? attn_lookup_bf16_auto(head_size, block_size, pl.grows)
+        : kv_dtype == B200_KV_FP8_E4M3 ? attn_lookup_bf16_e4m3(head_size, block_size, pl.grows)
+        : kv_dtype == B200_KV_FP8_E5M2 ? attn_lookup_bf16_e5m2(head_size, block_size, pl.grows)
+                                       : e;
+  } else {
+    set_error("Unsupported data type: query dtype %d (float32 queries are not instantiated yet)",
+              q_dtype);
+    return B200_ERR_UNSUPPORTED;
+  }
+  if (kv_dtype < 0 || kv_dtype > B200_KV_FP8_E5M2) {
+    set_error("Unsupported data type of kv cache: %d", kv_dtype);
+    return B200_ERR_UNSUPPORTED;
+  }
+  if (!e.launch) {
+    if (block_size != 8 && block_size != 16 && block_size != 32)
+      set_error("Unsupported block size: %d", block_size);
+    else
+      set_error("Unsupported head size: %d", head_size);
+    return B200_ERR_UNSUPPORTED;
+  }
+  pl.entry = e;
+
+  int num_sms = 148;
+  cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device);
+  pl.num_sms = num_sms;
+
+  // Pipeline geometry: aim for two resident CTAs per SM and >= 96 KiB of pages in flight per SM.
+  const int es = kv_dtype == B200_KV_AUTO ? 2 : 1;
+  const size_t stage_bytes = (size_t)2 * head_size * block_size * es;
+  pl.nwarps = knobs().warps.load();
+  if (pl.nwarps < 1) pl.nwarps = 4;
+  if (pl.nwarps > 8) pl.nwarps = 8;
+  int ns = knobs().stages.load();
+  if (ns <= 0) {
+    const size_t budget = 104 * 1024;  // per CTA, so that two CTAs fit in 227 KiB
+    ns = (int)(budget / ((size_t)pl.nwarps * stage_bytes));
+    if (ns > 8) ns = 8;
+    if (ns < 2) ns = 2;
+  }
+  if (ns > 32) ns = 32;
+  while (ns > 1 && e.smem(pl.nwarps, ns) > (size_t)227 * 1024) --ns;
+  pl.nstages = ns;
+  pl.smem = e.smem(pl.nwarps, ns);
+  B200_CHECK_ARG(pl.smem <= (size_t)227 * 1024, "shared memory plan does not fit (%zu bytes)",
+                 pl.smem);
+  pl.ctas_per_sm = e.occupancy(pl.nwarps, ns);
+  if (pl.ctas_per_sm < 1) pl.ctas_per_sm = 1;
+
+  // v1 context split = cluster size.  Pick the split that fills whole waves of the machine while
+  // leaving every CTA at least 2 pages per warp.
+  pl.cluster = 1;
+  if (version == 1) {
+    const int forced = knobs().cluster.load();
+    if (forced > 0) {
+      pl.cluster = forced;
+    } else {
+      const long long slots = (long long)num_sms * pl.ctas_per_sm;
+      const long long base = (long long)num_seqs * num_kv_heads * pl.gchunks;
+      const int max_pages = (max_seq_len + block_size - 1) / block_size;
+      double best = -1.0;
+      for (int s = 1; s <= 8; s *= 2) {
+        if (s > 1 && max_pages / s < 2 * pl.nwarps) break;
+        const long long n = base * s;
+        const long long waves = (n + slots - 1) / slots;
+        double eff = (double)n / (double)(waves * slots);
+        eff -= 0.01 * (s > 1 ? 1 : 0) + 0.002 * s;  // merging is not free: prefer smaller splits
+        if (eff > best + 1e-9) {
+          best = eff;
+          pl.cluster = s;
+        }
+      }
+    }
+  }
+  return B200_OK;
+}
+
+static int run_attention(int version, void* out, float* exp_sums, float* max_logits, void* tmp_out,
+                         const void* query, const void* key_cache, const void* value_cache,
+                         const int32_t* block_tables, const int32_t* seq_lens,
+                         const float* alibi_slopes, int num_seqs, int num_heads, int num_kv_heads,
+                         int head_size, int block_size, int max_seq_len,
+                         int max_num_blocks_per_seq, int max_num_partitions, int64_t q_stride,
+                         int64_t kv_block_stride, int64_t kv_head_stride, float scale,
+                         float k_scale, float v_scale, int q_dtype, int kv_dtype,
+                         const b200_blocksparse_t* bsp, int device, cudaStream_t stream) {
+  B200_CHECK_ARG(num_seqs >= 0 && head_size > 0 && block_size > 0 && max_seq_len >= 0,
+                 "paged_attention: bad sizes");
+  if (num_seqs == 0) return B200_OK;
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  int dev = device;
+  if (dev < 0) B200_CUDA_OK(cudaGetDevice(&dev));
+
+  Plan pl;
+  int rc = make_plan(pl, version, num_seqs, num_heads, num_kv_heads, head_size, block_size,
+                     max_seq_len, q_dtype, kv_dtype, dev);
+  if (rc != B200_OK) return rc;
+
+  const int es = kv_dtype == B200_KV_AUTO ? 2 : 1;
+  B200_CHECK_ARG((reinterpret_cast<uintptr_t>(key_cache) & 15) == 0 &&
+                     (reinterpret_cast<uintptr_t>(value_cache) & 15) == 0 &&
+                     (kv_block_stride * es) % 16 == 0 && (kv_head_stride * es) % 16 == 0,
+                 "paged_attention: KV cache base/strides must be 16-byte aligned");
+  B200_CHECK_ARG((reinterpret_cast<uintptr_t>(query) & 3) == 0 && q_stride % 2 == 0,
+                 "paged_attention: query rows must be 4-byte aligned");
+  B200_CHECK_ARG(kv_head_stride >= (int64_t)head_size * block_size,
+                 "paged_attention: kv_head_stride smaller than one page");
+  if (version == 2) {
+    const int need = (max_seq_len + kPartitionSize - 1) / kPartitionSize;
+    B200_CHECK_ARG(max_num_partitions >= need && max_num_partitions >= 1,
+                   "paged_attention_v2: scratch has %d partitions, need %d", max_num_partitions,
+                   need);
+    B200_CHECK_ARG(kPartitionSize % block_size == 0, "partition size not a multiple of block size");
+  }
+
+  AttnParams p{};
+  p.out = out;
+  p.exp_sums = exp_sums;
+  p.max_logits = max_logits;
+  p.tmp_out = tmp_out;
+  p.q = query;
+  p.k_cache = key_cache;
+  p.v_cache = value_cache;
+  p.block_tables = block_tables;
+  p.seq_lens = seq_lens;
+  p.alibi_slopes = alibi_slopes;
+  p.num_heads = num_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.group = num_heads / num_kv_heads;
+  p.gchunks = pl.gchunks;
+  p.max_blocks_per_seq = max_num_blocks_per_seq;
+  p.max_num_partitions = max_num_partitions;
+  p.partition_pages = version == 2 ? kPartitionSize / block_size : 0;
+  p.num_stages = pl.nstages;
+  p.q_stride = q_stride;
+  p.kv_block_stride = kv_block_stride;
+  p.kv_head_stride = kv_head_stride;
+  const float log2e = 1.4426950408889634f;
+  p.scale_log2 = scale * log2e * (kv_dtype == B200_KV_AUTO ? 1.f : k_scale);
+  p.out_scale = kv_dtype == B200_KV_AUTO ? 1.f : v_scale;
+  if (bsp && bsp->vert_stride > 1) {  // is_block_sparse (attention_kernels.cu:825)
+    B200_CHECK_ARG(bsp->block_size > 0, "blocksparse_block_size must be positive");
+    p.bs_enabled = 1;
+    p.bs_tp_rank = bsp->tp_rank;
+    p.bs_local_blocks = bsp->local_blocks;
+    p.bs_vert_stride = bsp->vert_stride;
+    p.bs_block_size = bsp->block_size;
+    p.bs_head_sliding_step = bsp->head_sliding_step;
+  }
+
+  const int splits = version == 2 ? max_num_partitions : pl.cluster;
+  B200_CHECK_ARG((long long)num_kv_heads * pl.gchunks <= 65535 && num_seqs <= 65535,
+                 "paged_attention: grid too large");
+  dim3 grid(splits, num_kv_heads * pl.gchunks, num_seqs);
+  rc = pl.entry.launch(p, grid, version == 2 ? 1 : pl.cluster, pl.nwarps, pl.nstages, dev, stream);
+  if (rc != B200_OK) return rc;
+
+  if (version == 2) {
+    const int64_t pairs = (int64_t)num_seqs * num_heads;
+    const unsigned blocks = (unsigned)((pairs + 3) / 4);
+    if (q_dtype == B200_DT_F16)
+      paged_attention_v2_reduce_kernel<__half><<<blocks, 128, 0, stream>>>(
+          static_cast<__half*>(out), exp_sums, max_logits, static_cast<const __half*>(tmp_out),
+          seq_lens, num_heads, head_size, max_num_partitions, pairs);
+    else
+      paged_attention_v2_reduce_kernel<__nv_bfloat16><<<blocks, 128, 0, stream>>>(
+          static_cast<__nv_bfloat16*>(out), exp_sums, max_logits,
+          static_cast<const __nv_bfloat16*>(tmp_out), seq_lens, num_heads, head_size,
+          max_num_partitions, pairs);
+    count_launch();
+    B200_CUDA_OK(cudaGetLastError());
+  }
+  return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_paged_attention_v1(void* out, const void* query, const void* key_cache,
+                                       const void* value_cache, const int32_t* block_tables,
+                                       const int32_t* seq_lens, const float* alibi_slopes,
+                                       int num_seqs, int num_heads, int num_kv_heads, int head_size,
+                                       int block_size, int max_seq_len, int max_num_blocks_per_seq,
+                                       int64_t q_stride, int64_t kv_block_stride,
+                                       int64_t kv_head_stride, float scale, float k_scale,
+                                       float v_scale, int q_dtype, int kv_dtype,
+                                       const b200_blocksparse_t* blocksparse, int device,
+                                       b200_stream_t stream) {
+  return run_attention(1, out, nullptr, nullptr, nullptr, query, key_cache, value_cache,
+                       block_tables, seq_lens, alibi_slopes, num_seqs, num_heads, num_kv_heads,
+                       head_size, block_size, max_seq_len, max_num_blocks_per_seq, 0, q_stride,
+                       kv_block_stride, kv_head_stride, scale, k_scale, v_scale, q_dtype, kv_dtype,
+                       blocksparse, device, (cudaStream_t)stream);
+}
+
+extern "C" int b200_paged_attention_v2(void* out, float* exp_sums, float* max_logits, void* tmp_out,
+                                       const void* query, const void* key_cache,
+                                       const void* value_cache, const int32_t* block_tables,
+                                       const int32_t* seq_lens, const float* alibi_slopes,
+                                       int num_seqs, int num_heads, int num_kv_heads, int head_size,
+                                       int block_size, int max_seq_len, int max_num_blocks_per_seq,
+                                       int max_num_partitions, int64_t q_stride,
+                                       int64_t kv_block_stride, int64_t kv_head_stride, float scale,
+                                       float k_scale, float v_scale, int q_dtype, int kv_dtype,
+                                       const b200_blocksparse_t* blocksparse, int device,
+                                       b200_stream_t stream) {
+  B200_CHECK_ARG(exp_sums && max_logits && tmp_out, "paged_attention_v2: scratch tensors required");
+  return run_attention(2, out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
+                       block_tables, seq_lens, alibi_slopes, num_seqs, num_heads, num_kv_heads,
+                       head_size, block_size, max_seq_len, max_num_blocks_per_seq,
+                       max_num_partitions, q_stride, kv_block_stride, kv_head_stride, scale,
+                       k_scale, v_scale, q_dtype, kv_dtype, blocksparse, device,
+                       (cudaStream_t)stream);
+}
+
+extern "C" int b200_paged_attention_plan(int version, int num_seqs, int num_heads, int num_kv_heads,
+                                         int head_size, int block_size, int max_seq_len,
+                                         int q_dtype, int kv_dtype, int device,
+                                         b200_attn_plan_t* plan) {
+  B200_CHECK_ARG(plan != nullptr, "plan must not be null");
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  int dev = device;
+  if (dev < 0) B200_CUDA_OK(cudaGetDevice(&dev));
+  Plan pl;
+  int rc = make_plan(pl, version, num_seqs, num_heads, num_kv_heads, head_size, block_size,
+                     max_seq_len, q_dtype, kv_dtype, dev);
+  if (rc != B200_OK) return rc;
+  plan->cluster_size = pl.cluster;
+  plan->num_warps = pl.nwarps;
+  plan->num_stages = pl.nstages;
+  plan->smem_bytes = (int32_t)pl.smem;
+  plan->ctas_per_sm = pl.ctas_per_sm;
+  plan->grid_x = version == 2 ? (max_seq_len + kPartitionSize - 1) / kPartitionSize : pl.cluster;
+  plan->grid_y = num_kv_heads * pl.gchunks;
+  plan->grid_z = num_seqs;
+  return B200_OK;
+}
+
+extern "C" void b200_set_attn_tuning(int warps, int stages, int cluster) {
+  knobs().warps.store(warps);
+  knobs().stages.store(stages);
+  knobs().cluster.store(cluster);
+}

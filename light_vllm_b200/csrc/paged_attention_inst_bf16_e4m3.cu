@@ -1,0 +1,6 @@
+// Instantiations of the paged-attention kernel for query dtype bf16, KV cache format e4m3.
+#define INST_T __nv_bfloat16
+#define INST_KV B200_KV_FP8_E4M3
+#define INST_KV_IS_AUTO 0
+#define INST_NAME attn_lookup_bf16_e4m3
+#include "paged_attention_inst.inc"
