@@ -1,0 +1,434 @@
+#!/usr/bin/env python
+"""bench.py -- paged-attention decode hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config c2|c3|c4] [--impl b200|reference]
+
+A *step* is one pass of the hot path over one decode batch: for each of ``--layers`` KV pools
+(the layers of a model; each pool is larger than L2, so KV reads always come from HBM):
+``reshape_and_cache`` of the batch's newest token, then ``paged_attention`` over the whole context.
+Default workload = BASELINE.json configs[1] (c2): fp16, 32 q / 8 kv heads, head 128, block 16,
+batch 64, ctx 2048, paged_attention_v1.
+
+Printed JSON (one line, rank 0):
+  value      KV bytes read per second, whole job, inputs resident in HBM (device timed, max over ranks)
+  e2e        same metric through the attention plugin with HOST (pinned) inputs: per step the
+             H2D copy of q/k/v + metadata and the D2H read of the output are inside the timed region
+  roofline   the attention kernel alone: algorithmic bytes per launch / CUDA-event launch time
+  cpu_baseline  the reference's own CPU kernels (oracle/_ref/libref_cpu.so) or the C oracle port,
+             timed on this box's host cores on a bounded sample
+Multi-GPU: launched by torchrun, one process per GPU; sequences are sharded (each rank owns its
+pools and block tables), no data-path collective; ``scaling`` = "weak".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    # name: dtype, kv_cache_dtype, H, KH, D, BS, B, ctx, version, label
+    "c2": dict(dtype="float16", kv="auto", H=32, KH=8, D=128, BS=16, B=64, ctx=2048, version=1,
+               label="paged_attention_v1 microbench fp16: 32 q-heads/8 kv-heads, head_dim 128, "
+                     "block_size 16, batch 64, ctx 2048"),
+    "c3": dict(dtype="bfloat16", kv="auto", H=32, KH=8, D=128, BS=16, B=256, ctx=4096, version=2,
+               label="Llama-3-8B-shaped decode bf16, batch 256, ctx 4096, paged_attention_v2"),
+    "c4": dict(dtype="bfloat16", kv="fp8", H=28, KH=4, D=128, BS=16, B=512, ctx=8192, version=1,
+               label="fp8_e4m3 KV cache Qwen2-7B-shaped decode, batch 512, ctx 8192"),
+}
+
+
+def kv_bytes_per_layer(c):
+    es = 1 if c["kv"] != "auto" else 2
+    return c["B"] * c["ctx"] * c["KH"] * c["D"] * 2 * es
+
+
+def algorithmic_bytes_attention(c):
+    """KV read + q + out + block-table + seq_lens bytes of one attention launch."""
+    es = 1 if c["kv"] != "auto" else 2
+    kv = c["B"] * c["ctx"] * c["KH"] * c["D"] * 2 * es
+    qo = 2 * c["B"] * c["H"] * c["D"] * 2
+    bt = 4 * c["B"] * ((c["ctx"] + c["BS"] - 1) // c["BS"])
+    return kv + qo + bt + 4 * c["B"]
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.proc, self.lines, self.index = None, [], index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms",
+                 "100", "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# CPU side: the reference's own CPU kernels (oracle/_ref/libref_cpu.so) or the C oracle port.
+# The only places bench.py executes anything under oracle/: cpu_baseline and --impl reference.
+# --------------------------------------------------------------------------------------------
+def cpu_step_fn(c, sample_B):
+    """Returns (step_fn, kind, dtype_name, cores).  One step = reshape_and_cache + attention on a
+    batch slice of ``sample_B`` sequences of the same ctx (the CPU path has no fp16/fp8: those
+    configs run in bf16, same bytes per element as fp16; stated in `sample`)."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from kv_util import make_case, v2_scratch
+    from oracle import ref
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    use_ref = ref.have_ref_cpu()
+    dtype = torch.bfloat16 if use_ref else getattr(torch, c["dtype"])
+    H, KH, D, BS, ctx = c["H"], c["KH"], c["D"], c["BS"], c["ctx"]
+    case = make_case(sample_B, H, KH, D, BS, [ctx] * sample_B, dtype, seed=0)
+    g = torch.Generator().manual_seed(1)
+    key = ((torch.rand(sample_B, KH, D, generator=g) * 2 - 1) * case["scale"]).to(dtype)
+    value = ((torch.rand(sample_B, KH, D, generator=g) * 2 - 1) * case["scale"]).to(dtype)
+    slots = torch.tensor([int(case["block_tables"][i, (ctx - 1) // BS]) * BS + (ctx - 1) % BS
+                          for i in range(sample_B)], dtype=torch.int64)
+    out = torch.empty_like(case["query"])
+    if use_ref:
+        mod, kind = ref.ref_cpu(), "reference"
+    else:
+        from oracle import oracle as mod
+        kind = "port"
+    attn_tail = (case["query"], case["key_cache"], case["value_cache"], KH, case["scale"],
+                 case["block_tables"], case["seq_lens"], BS, ctx, None, "auto", 1.0, 1.0, 0, 0, 0,
+                 64, 0)
+    scratch = v2_scratch(case)
+
+    def step():
+        mod.reshape_and_cache(key, value, case["key_cache"], case["value_cache"], slots, "auto",
+                              1.0, 1.0)
+        if c["version"] == 1:
+            mod.paged_attention_v1(out, *attn_tail)
+        else:
+            mod.paged_attention_v2(out, *scratch, *attn_tail)
+
+    return step, kind, str(dtype).replace("torch.", ""), cores
+
+
+def time_cpu(c, budget_s, sample_B=None, steps=None, warmup=1):
+    # ~512 MiB of KV per step (well above the host's last-level cache), never more than the batch
+    per_seq = c["ctx"] * c["KH"] * c["D"] * 2 * 2
+    sample_B = sample_B or max(1, min(c["B"], (512 << 20) // per_seq))
+    step, kind, dt, cores = cpu_step_fn(c, sample_B)
+    for _ in range(warmup):
+        step()
+    times = []
+    t_end = time.perf_counter() + budget_s
+    while (steps is None and time.perf_counter() < t_end and len(times) < 50) or \
+            (steps is not None and len(times) < steps):
+        t0 = time.perf_counter()
+        step()
+        times.append(time.perf_counter() - t0)
+    es = 2
+    kv_bytes = sample_B * c["ctx"] * c["KH"] * c["D"] * 2 * es
+    best, mean = min(times), sum(times) / len(times)
+    return dict(kind=kind, cores=cores, dtype=dt, sample_B=sample_B, best_s=best, mean_s=mean,
+                n=len(times), kv_bytes=kv_bytes)
+
+
+def run_reference_arm(args, c):
+    """--impl reference: the reference's CPU implementation of the path on this box's host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    r = time_cpu(c, budget_s=1e9, steps=args.steps, warmup=args.warmup)
+    gbs = r["kv_bytes"] / r["mean_s"] / 1e9
+    sample = (f"{r['sample_B']} of {c['B']} sequences x ctx {c['ctx']}, 1 layer pool, {r['dtype']} "
+              f"(CPU path has no fp16/fp8), reshape_and_cache + paged_attention_v{c['version']} "
+              f"per step, {r['n']} steps, all {r['cores']} host threads")
+    line = {
+        "impl": "reference", "metric": "paged_attn_kv_read_GBps", "value": round(gbs, 3),
+        "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(r["mean_s"] * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": r["dtype"], "data": "synthetic",
+        "config": {"workload": c["label"], "name": args.config},
+        "decode_tokens_per_s_per_layer": round(r["sample_B"] / r["mean_s"], 1),
+        "cpu_baseline": {"value": round(gbs, 3), "unit": "GB/s", "cores": r["cores"],
+                         "kind": r["kind"], "sample": sample},
+        "e2e": {"value": round(gbs, 3), "unit": "GB/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------
+# B200 arm
+# --------------------------------------------------------------------------------------------
+def run_b200_arm(args, c):
+    import torch
+    import torch.distributed as dist
+
+    from light_vllm_b200 import _custom_ops as ops
+    from light_vllm_b200 import _lib
+    from light_vllm_b200.attention import (PagedAttention, PagedB200AttentionBackend,
+                                           PagedB200AttentionMetadata)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback exists)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    dtype = getattr(torch, c["dtype"])
+    kv = c["kv"]
+    cache_dtype = dtype if kv == "auto" else torch.uint8
+    H, KH, D, BS, B, ctx, L = c["H"], c["KH"], c["D"], c["BS"], c["B"], c["ctx"], args.layers
+    scale = D ** -0.5
+    k_scale = v_scale = 1.0 if kv == "auto" else 0.05
+    blocks_per_seq = (ctx + BS - 1) // BS
+    NB = B * blocks_per_seq + 64
+    torch.manual_seed(1234 + rank)
+
+    # ---- this rank's shard: its own pools, block tables and sequences (sequence sharding) ----
+    shape = PagedB200AttentionBackend.get_kv_cache_shape(NB, BS, KH, D)
+    pools = []
+    for _ in range(L):
+        if cache_dtype == torch.uint8:
+            src = torch.empty(shape, dtype=dtype, device=dev).uniform_(-scale, scale)
+            pool = torch.empty(shape, dtype=torch.uint8, device=dev)
+            ops.convert_fp8(pool, src, k_scale, "fp8")
+            del src
+        else:
+            pool = torch.empty(shape, dtype=dtype, device=dev).uniform_(-scale, scale)
+        pools.append(pool)
+    split = [PagedAttention.split_kv_cache(p, KH, D) for p in pools]
+    block_tables_h = torch.randperm(NB)[:B * blocks_per_seq].view(B, blocks_per_seq).int().pin_memory()
+    seq_lens_h = torch.full((B,), ctx, dtype=torch.int32).pin_memory()
+    slots_h = (block_tables_h[:, (ctx - 1) // BS].long() * BS + (ctx - 1) % BS).pin_memory()
+    qkv_h = torch.empty(B, (H + 2 * KH) * D, dtype=dtype).uniform_(-scale, scale).pin_memory()
+    out_h = torch.empty(B, H * D, dtype=dtype).pin_memory()
+
+    block_tables, seq_lens, slots = block_tables_h.to(dev), seq_lens_h.to(dev), slots_h.to(dev)
+    qkv = qkv_h.to(dev)
+    q = qkv[:, :H * D].view(B, H, D)
+    k = qkv[:, H * D:(H + KH) * D].view(B, KH, D)
+    v = qkv[:, (H + KH) * D:].view(B, KH, D)
+    out = torch.empty(B, H, D, dtype=dtype, device=dev)
+    P = (ctx + 511) // 512
+    scratch = (torch.empty(B, H, P, dtype=torch.float32, device=dev),
+               torch.empty(B, H, P, dtype=torch.float32, device=dev),
+               torch.empty(B, H, P, D, dtype=dtype, device=dev))
+
+    def attention(l):
+        kc, vc = split[l]
+        if c["version"] == 1:
+            ops.paged_attention_v1(out, q, kc, vc, KH, scale, block_tables, seq_lens, BS, ctx, None,
+                                   kv, k_scale, v_scale)
+        else:
+            ops.paged_attention_v2(out, *scratch, q, kc, vc, KH, scale, block_tables, seq_lens, BS,
+                                   ctx, None, kv, k_scale, v_scale)
+
+    def device_step():
+        for l in range(L):
+            kc, vc = split[l]
+            ops.reshape_and_cache(k, v, kc, vc, slots, kv, k_scale, v_scale)
+            attention(l)
+
+    # ---- the same step through the plugin, from HOST buffers ----
+    impl = PagedB200AttentionBackend.get_impl_cls()(H, D, scale, KH, None, None, kv)
+
+    def e2e_step():
+        x = qkv_h.to(dev, non_blocking=True)
+        meta = PagedB200AttentionMetadata(
+            num_prefills=0, num_prefill_tokens=0, num_decode_tokens=B, slot_mapping=slots_h,
+            seq_lens=None, seq_lens_tensor=seq_lens_h, max_query_len=1, max_prefill_seq_len=0,
+            max_decode_seq_len=ctx, query_start_loc=None, seq_start_loc=None,
+            context_lens_tensor=None, block_tables=block_tables_h, use_cuda_graph=False)
+        meta.to(dev, non_blocking=True)
+        xq, xk, xv = x[:, :H * D], x[:, H * D:(H + KH) * D], x[:, (H + KH) * D:]
+        o = None
+        for l in range(L):
+            o = impl.forward(xq, xk, xv, pools[l], meta, k_scale, v_scale)
+        out_h.copy_(o, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    h2d = qkv_h.numel() * qkv_h.element_size() + slots_h.numel() * 8 + seq_lens_h.numel() * 4 + \
+        block_tables_h.numel() * 4
+    d2h = out_h.numel() * out_h.element_size()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        """n calls of fn between a barrier+sync on both sides; device time by CUDA events on the
+        launching (current) stream; max over ranks."""
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms
+
+    for _ in range(max(args.warmup, 3)):
+        device_step()
+    sampler = ClockSampler(local_rank)
+    n0 = _lib.launch_count()
+    sampler.start()
+    ms_total = timed(device_step, args.steps)
+    clocks = sampler.stop()
+    launches = _lib.launch_count() - n0
+
+    for _ in range(max(args.warmup, 3)):
+        e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+
+    # attention kernel alone, for the roofline (cycling pools: every launch reads cold KV)
+    reps = max(20, args.steps)
+    for l in range(L):
+        attention(l)
+    counter = [0]
+
+    def attn_only():
+        attention(counter[0] % L)
+        counter[0] += 1
+
+    ms_attn = timed(attn_only, reps) / reps
+    return dict(rank=rank, world=world, ms_total=ms_total, ms_e2e=ms_e2e, ms_attn=ms_attn,
+                clocks=clocks, launches=launches, h2d=h2d, d2h=d2h, L=L,
+                plan=_lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, local_rank),
+                dist=dist if world > 1 else None)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
+    ap.add_argument("--layers", type=int, default=4,
+                    help="KV pools cycled per step (each > L2; a model's layers)")
+    ap.add_argument("--cpu-budget", type=float, default=12.0,
+                    help="seconds of CPU work for the cpu_baseline leg (0 disables)")
+    args = ap.parse_args()
+    c = CONFIGS[args.config]
+    if args.impl == "reference":
+        run_reference_arm(args, c)
+        return
+
+    r = run_b200_arm(args, c)
+    world = r["world"]
+    cpu = None
+    if r["rank"] == 0 and world == 1 and args.cpu_budget > 0:
+        try:
+            cpu = time_cpu(c, budget_s=args.cpu_budget)
+        except Exception as e:  # the baseline is reported, never required for the GPU numbers
+            cpu = {"error": repr(e)}
+    if r["rank"] == 0:
+        L = r["L"]
+        kvb = kv_bytes_per_layer(c)
+        step_s = r["ms_total"] / 1e3 / args.steps
+        e2e_s = r["ms_e2e"] / 1e3 / args.steps
+        value = world * L * kvb / step_s / 1e9
+        e2e = world * L * kvb / e2e_s / 1e9
+        peak, peak_src = measured_peak_gbs()
+        achieved = algorithmic_bytes_attention(c) / (r["ms_attn"] / 1e3) / 1e9
+        line = {
+            "metric": "paged_attn_kv_read_GBps", "value": round(value, 1), "unit": "GB/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": round(step_s * 1e3, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f16" if c["dtype"] == "float16" else "bf16",
+            "data": "synthetic",
+            "config": {"workload": c["label"], "name": args.config, "kv_cache_dtype": c["kv"],
+                       "layer_pools_per_step": L, "kv_bytes_per_pool": kvb,
+                       "l2": f"inputs larger than L2: {L} pools x {kvb >> 20} MiB cycled",
+                       "sharding": "by sequence; each rank owns its pools and block tables",
+                       "plan": r["plan"]},
+            "frac_of_hbm_peak": round(value / world / peak, 4),
+            "decode_tokens_per_s_per_layer": round(world * c["B"] * L / step_s, 1),
+            "e2e": {"value": round(e2e, 1), "unit": "GB/s", "h2d_bytes_per_step": r["h2d"],
+                    "d2h_bytes_per_step": r["d2h"], "ms_per_step": round(e2e_s * 1e3, 4),
+                    "api": "PagedB200AttentionImpl.forward per layer pool, pinned host q/k/v + "
+                           "metadata in, output read back"},
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
+                         "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None,
+                         "kernel": f"paged_attention_v{c['version']} (attention launch alone, "
+                                   f"{algorithmic_bytes_attention(c)} algorithmic bytes)",
+                         "us_per_launch": round(r["ms_attn"] * 1e3, 2), "peak_source": peak_src,
+                         "frac_of_8TBps_datasheet": round(achieved / 8000.0, 4)},
+            "clocks": r["clocks"], "gpu_launches": r["launches"],
+        }
+        if cpu is not None and "error" not in cpu:
+            gbs = cpu["kv_bytes"] / cpu["best_s"] / 1e9
+            line["cpu_baseline"] = {
+                "value": round(gbs, 3), "unit": "GB/s", "cores": cpu["cores"], "kind": cpu["kind"],
+                "sample": f"{cpu['sample_B']} of {c['B']} sequences x ctx {c['ctx']}, 1 layer pool, "
+                          f"{cpu['dtype']} (CPU path has no fp16/fp8), reshape_and_cache + "
+                          f"paged_attention_v{c['version']}, best of {cpu['n']} "
+                          f"({cpu['best_s'] * 1e3:.1f} ms)"}
+        elif cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if r["dist"] is not None:
+        r["dist"].barrier()
+        r["dist"].destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

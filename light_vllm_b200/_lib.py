@@ -1,0 +1,109 @@
+"""Loader for the native libraries of the B200 paged-KV hot path.
+
+Two shared objects live next to this file (built in-tree by ``csrc/Makefile`` or
+``__graft_entry__.build()``):
+
+* ``libb200_paged.so`` -- the C-ABI library declared in ``include/b200_paged.h`` (hand-written
+  sm_100a kernels; no torch types cross that boundary);
+* ``_C.so`` -- the thin torch binding that registers ``torch.ops._C``, ``torch.ops._C_cache_ops``
+  and ``torch.ops._C_cuda_utils`` with the reference's schemas
+  (reference: ``csrc/torch_bindings.cpp:24-48,227-280``) and forwards to the C ABI.
+
+There is no CPU or pure-PyTorch fallback: if either library is missing, importing this module
+raises, and every op raises without a CUDA device.
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200_paged.so")
+BINDING_PATH = os.path.join(_HERE, "_C.so")
+
+# Every symbol include/b200_paged.h declares (checked by tests/test_abi.py).
+ABI_SYMBOLS = (
+    "b200_last_error",
+    "b200_abi_version",
+    "b200_parse_kv_cache_dtype",
+    "b200_paged_attention_v1",
+    "b200_paged_attention_v2",
+    "b200_reshape_and_cache",
+    "b200_reshape_and_cache_flash",
+    "b200_copy_blocks",
+    "b200_swap_blocks",
+    "b200_convert_fp8",
+    "b200_get_device_attribute",
+    "b200_get_max_shared_memory_per_block_device_attribute",
+    "b200_paged_attention_plan",
+    "b200_set_attn_tuning",
+    "b200_set_swap_mode",
+    "b200_launch_count",
+)
+
+
+class AttnPlan(ctypes.Structure):
+    """Mirror of ``b200_attn_plan_t``."""
+    _fields_ = [(n, ctypes.c_int32) for n in ("cluster_size", "num_warps", "num_stages",
+                                                "smem_bytes", "ctas_per_sm", "grid_x", "grid_y",
+                                                "grid_z")]
+
+
+def _load():
+    for p in (LIB_PATH, BINDING_PATH):
+        if not os.path.exists(p):
+            raise ImportError(
+                f"{p} is missing: build the native extension first "
+                "(`make -C light_vllm_b200/csrc` or `python -c 'import __graft_entry__ as g; "
+                "g.build()'`). light_vllm_b200 has no CPU / PyTorch fallback.")
+    lib = ctypes.CDLL(LIB_PATH, mode=ctypes.RTLD_GLOBAL)
+    lib.b200_last_error.restype = ctypes.c_char_p
+    lib.b200_launch_count.restype = ctypes.c_int64
+    lib.b200_get_device_attribute.restype = ctypes.c_int64
+    lib.b200_get_device_attribute.argtypes = [ctypes.c_int64, ctypes.c_int64]
+    lib.b200_get_max_shared_memory_per_block_device_attribute.restype = ctypes.c_int64
+    lib.b200_get_max_shared_memory_per_block_device_attribute.argtypes = [ctypes.c_int64]
+    lib.b200_parse_kv_cache_dtype.argtypes = [ctypes.c_char_p]
+    lib.b200_set_attn_tuning.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    lib.b200_set_attn_tuning.restype = None
+    lib.b200_set_swap_mode.argtypes = [ctypes.c_int]
+    lib.b200_set_swap_mode.restype = None
+    lib.b200_paged_attention_plan.argtypes = [ctypes.c_int] * 10 + [ctypes.POINTER(AttnPlan)]
+    torch.ops.load_library(BINDING_PATH)
+    return lib
+
+
+lib = _load()
+
+
+def launch_count() -> int:
+    """Kernels launched by libb200_paged.so from this process (bench.py's ``gpu_launches``)."""
+    return int(lib.b200_launch_count())
+
+
+def last_error() -> str:
+    return lib.b200_last_error().decode()
+
+
+_DT = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
+
+
+def attention_plan(version, num_seqs, num_heads, num_kv_heads, head_size, block_size, max_seq_len,
+                   dtype, kv_cache_dtype="auto", device=0) -> dict:
+    """Launch geometry the library would pick (needs a CUDA device)."""
+    plan = AttnPlan()
+    kv = lib.b200_parse_kv_cache_dtype(kv_cache_dtype.encode())
+    rc = lib.b200_paged_attention_plan(version, num_seqs, num_heads, num_kv_heads, head_size,
+                                       block_size, max_seq_len, _DT[dtype], kv, device,
+                                       ctypes.byref(plan))
+    if rc != 0:
+        raise RuntimeError(last_error())
+    return {n: getattr(plan, n) for n, _ in AttnPlan._fields_}
+
+
+def set_attn_tuning(warps=0, stages=0, cluster=0) -> None:
+    lib.b200_set_attn_tuning(int(warps), int(stages), int(cluster))
+
+
+def set_swap_mode(mode=0) -> None:
+    lib.b200_set_swap_mode(int(mode))

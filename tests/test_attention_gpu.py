@@ -1,0 +1,126 @@
+"""GPU parity: paged_attention_v1/v2 (product, through torch.ops._C -> C ABI) vs the CPU oracle
+(oracle/paged_oracle.c), the fp64 ground truth, and -- when oracle/_ref/libref_cuda.so travelled
+with the snapshot -- the reference's own CUDA kernels recompiled for sm_100a.
+
+Tolerances are BASELINE.json's: max-abs 2e-3 (fp16), 1e-2 (bf16) against the reference op.
+"""
+import pytest
+import torch
+
+from kv_util import make_case, naive_attention, to_device, v2_scratch
+
+pytestmark = pytest.mark.gpu
+TOL = {torch.float16: 2e-3, torch.bfloat16: 1e-2}
+TAIL = (0, 0, 0, 64, 0)  # tp_rank, local_blocks, vert_stride, bs_block_size, head_sliding_step
+
+
+def attn_args(c, kv="auto", ks=1.0, vs=1.0, alibi=None, tail=TAIL):
+    return (c["query"], c["key_cache"], c["value_cache"], c["num_kv_heads"], c["scale"],
+            c["block_tables"], c["seq_lens"], c["block_size"], c["max_seq_len"], alibi, kv, ks, vs,
+            *tail)
+
+
+def run_v1(mod, c, **kw):
+    out = torch.full_like(c["query"].contiguous(), float("nan"))
+    mod.paged_attention_v1(out, *attn_args(c, **kw))
+    return out
+
+
+def run_v2(mod, c, **kw):
+    out = torch.full_like(c["query"].contiguous(), float("nan"))
+    es, ml, tmp = v2_scratch(c, device=c["query"].device)
+    mod.paged_attention_v2(out, es, ml, tmp, *attn_args(c, **kw))
+    return out
+
+
+def check(ops, oracle, c, dtype, version, **kw):
+    g = to_device(c, "cuda")
+    run_gpu = run_v1 if version == 1 else run_v2
+    got = run_gpu(ops, g, **{k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in kw.items()})
+    torch.cuda.synchronize()
+    want = (run_v1 if version == 1 else run_v2)(oracle, c, **kw)
+    live = c["seq_lens"] > 0
+    assert not torch.isnan(got.float().cpu()[live]).any(), "NaN in output"
+    err = (got.float().cpu()[live] - want.float()[live]).abs().max().item() if live.any() else 0.0
+    assert err <= TOL[dtype], f"v{version} {dtype}: max-abs {err} vs oracle"
+    return got
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("version", [1, 2])
+def test_mixed_lengths_gqa(ops, oracle, dtype, version):
+    # config-2 shape (32 q / 8 kv heads, D 128, BS 16) at oracle-friendly batch; ragged lengths
+    lens = [1, 2, 15, 16, 17, 100, 511, 512, 513, 1024, 1500, 2048]
+    c = make_case(len(lens), 32, 8, 128, 16, lens, dtype, seed=3, nan_padding=True)
+    got = check(ops, oracle, c, dtype, version)
+    gt = naive_attention(c)
+    assert (got.double().cpu() - gt).abs().max().item() <= TOL[dtype]
+
+
+@pytest.mark.parametrize("heads", [(8, 8), (8, 1), (28, 4), (14, 2), (40, 2)])
+@pytest.mark.parametrize("version", [1, 2])
+def test_head_groupings(ops, oracle, heads, version):
+    H, KH = heads  # MHA, MQA, GQA-7 (Qwen2-7B), GQA-7 (Qwen2-0.5B), GQA-20 (> 16 rows)
+    lens = [33, 700, 129, 1, 600]
+    c = make_case(len(lens), H, KH, 128 if H != 14 else 64, 16, lens, torch.float16, seed=H)
+    check(ops, oracle, c, torch.float16, version)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_strided_query_and_alibi(ops, oracle, dtype):
+    lens = [40, 333, 1000]
+    c = make_case(len(lens), 16, 4, 128, 16, lens, dtype, seed=5, q_pad=256)
+    alibi = torch.tensor([2.0 ** (-(i + 1) / 2) for i in range(16)], dtype=torch.float32)
+    for version in (1, 2):
+        check(ops, oracle, c, dtype, version, alibi=alibi)
+
+
+def test_single_dominant_logit(ops, oracle):
+    # adversarial softmax: one token's logit dwarfs the rest
+    lens = [700, 64]
+    c = make_case(len(lens), 8, 2, 128, 16, lens, torch.float16, seed=6)
+    blk = int(c["block_tables"][0, 20])
+    c["key_cache"][blk, :, :, 3, :] = 4.0
+    c["query"][0] = 1.0
+    for version in (1, 2):
+        check(ops, oracle, c, torch.float16, version)
+
+
+def test_empty_batch_and_zero_len(ops, oracle):
+    c = make_case(3, 8, 2, 128, 16, [0, 5, 0], torch.float16, seed=7)
+    check(ops, oracle, c, torch.float16, 1)
+    check(ops, oracle, c, torch.float16, 2)
+    g = to_device(make_case(1, 8, 2, 128, 16, [5], torch.float16), "cuda")
+    empty = dict(g)
+    empty["query"] = g["query"][:0]
+    empty["block_tables"] = g["block_tables"][:0]
+    empty["seq_lens"] = g["seq_lens"][:0]
+    out = torch.empty_like(empty["query"])
+    ops.paged_attention_v1(out, *attn_args(empty))  # must be a no-op, not an error
+
+
+def test_vs_reference_cuda_kernels(ops):
+    """Differential test against the reference's own CUDA kernels (authoritative for fp16)."""
+    from oracle import ref
+    if not ref.have_ref_cuda():
+        pytest.skip("oracle/_ref/libref_cuda.so not built")
+    rC, _ = ref.ref_cuda()
+    for dtype in (torch.float16, torch.bfloat16):
+        lens = [1, 17, 512, 513, 2048, 1999, 640, 3000]
+        g = to_device(make_case(len(lens), 32, 8, 128, 16, lens, dtype, seed=11, nan_padding=True), "cuda")
+        for version in (1, 2):
+            run = run_v1 if version == 1 else run_v2
+            got, want = run(ops, g), run(rC, g)
+            torch.cuda.synchronize()
+            err = (got.float() - want.float()).abs().max().item()
+            assert err <= TOL[dtype], f"v{version} {dtype}: max-abs {err} vs reference CUDA kernel"
+
+
+def test_unsupported_raises(ops):
+    g = to_device(make_case(1, 8, 2, 128, 16, [5], torch.float16), "cuda")
+    out = torch.empty_like(g["query"])
+    with pytest.raises(RuntimeError, match="Unsupported"):
+        ops.paged_attention_v1(out, *attn_args(g, kv="int4"))
+    bad = dict(g, block_size=24)
+    with pytest.raises(RuntimeError, match="block size"):
+        ops.paged_attention_v1(out, *attn_args(bad))
