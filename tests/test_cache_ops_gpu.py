@@ -100,7 +100,7 @@ def test_copy_blocks(ops, oracle, cache_dtype, pinned_mapping):
     for a, b in zip(got, want):
         assert torch.equal(raw(a), b)
     ops.copy_blocks([p[0] for p in got], [p[1] for p in got], mapping[:0].cuda())  # empty mapping: no-op
-    ops.copy_blocks([], [], m)
+    ops.copy_blocks([], [], mapping.cuda())  # no layers: no-op
 
 
 @pytest.mark.parametrize("direction", ["d2h", "h2d", "d2d"])
