@@ -84,9 +84,42 @@ struct MmaType<T, B200_KV_FP8_E5M2> {
 
 template <int KV>
 __device__ __forceinline__ uint32_t fp8x2_to_f16x2(uint16_t v) {
-  constexpr __nv_fp8_interpretation_t kind = (KV == B200_KV_FP8_E5M2) ? __NV_E5M2 : __NV_E4M3;
-  __half2_raw h = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)v, kind);
-  return (uint32_t)h.x | ((uint32_t)h.y << 16);
+  uint32_t r;
+  if constexpr (KV == B200_KV_FP8_E5M2)
+    asm("cvt.rn.f16x2.e5m2x2 %0, %1;" : "=r"(r) : "h"(v));
+  else
+    asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(r) : "h"(v));
+  return r;
+}
+// Four fp8 bytes -> two f16x2 registers (bytes 0,1 -> lo; bytes 2,3 -> hi).  Written so that ptxas
+// feeds the two halves of `w` to F2FP through its .H0/.H1 operand selectors: no PRMT/unpack
+// instructions (the cuda_fp8.h struct round trip cost ~3 PRMT per conversion, see
+// profiles/r1_c4_fp8_before.md).
+template <int KV>
+__device__ __forceinline__ void fp8x4_to_f16x2x2(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  if constexpr (KV == B200_KV_FP8_E5M2)
+    asm("{\n.reg .b16 a, b;\nmov.b32 {a, b}, %2;\ncvt.rn.f16x2.e5m2x2 %0, a;\n"
+        "cvt.rn.f16x2.e5m2x2 %1, b;\n}" : "=r"(lo), "=r"(hi) : "r"(w));
+  else
+    asm("{\n.reg .b16 a, b;\nmov.b32 {a, b}, %2;\ncvt.rn.f16x2.e4m3x2 %0, a;\n"
+        "cvt.rn.f16x2.e4m3x2 %1, b;\n}" : "=r"(lo), "=r"(hi) : "r"(w));
+}
+
+// Token (within the page) of the score this thread holds in S-accumulator n-tile `nt`, column pair
+// of lane-quad index `qq`, element `e`; equally the token whose K row the lane with column
+// c = 2*qq + e supplies to that n-tile.
+//   16-bit caches / 8-token pages: the natural order, token = 8*nt + c.
+//   fp8 caches with >= 16-token pages: within each 16-token group the columns are permuted so that
+//   a thread's four scores (tiles 2kk, 2kk+1) are the four CONSECUTIVE tokens 4*qq..4*qq+3.  P.V
+//   then needs V[d][4*qq..4*qq+3] = one 32-bit shared load per d-tile instead of two 16-bit ones,
+//   and both K-row sets {0,1,4,5,10,11,14,15} / {2,3,6,7,8,9,12,13} still cover all 8 16-byte
+//   bank groups, so the K loads stay conflict-free.
+template <int KV, int BS>
+__device__ __forceinline__ int page_token(int nt, int qq, int e) {
+  if constexpr (KV != B200_KV_AUTO && BS >= 16)
+    return (nt >> 1) * 16 + 4 * qq + 2 * ((nt & 1) ^ (qq >> 1)) + e;
+  else
+    return nt * 8 + 2 * qq + e;
 }
 
 // One KV page (BS tokens) against the warp's q-group: S = QK^T, online softmax, O += P V.
@@ -140,18 +173,21 @@ __device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
       }
     }
   } else {
-    // fp8 K page layout [D/16][BS][16].  Lane (n = lane/4, q4) reads 4 bytes: d = 16ks + 4*q4 + 0..3
-    // of token 8nt + n; (d0,d1) -> b0, (d2,d3) -> b1.  Q fragments are loaded with the matching
-    // d permutation (see load_q).
-    const uint32_t base = k_smem + (uint32_t)((lane >> 2) * 16 + q4 * 4);
+    // fp8 K page layout [D/16][BS][16].  Lane (column c = lane/4, q4) reads 4 bytes:
+    // d = 16ks + 4*q4 + 0..3 of token page_token(nt, c/2, c%2); (d0,d1) -> b0, (d2,d3) -> b1.
+    // Q fragments are loaded with the matching d permutation (see load_q).
+    const int c = lane >> 2;
+    uint32_t koff[NT];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+      koff[nt] = k_smem + (uint32_t)(page_token<KV, BS>(nt, c >> 1, c & 1) * 16 + q4 * 4);
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) {
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
-        uint32_t w;
-        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(base + (uint32_t)(ks * BS * 16 + nt * 8 * 16)));
-        const uint32_t b0 = fp8x2_to_f16x2<KV>((uint16_t)(w & 0xffffu));
-        const uint32_t b1 = fp8x2_to_f16x2<KV>((uint16_t)(w >> 16));
+        uint32_t w, b0, b1;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(koff[nt] + (uint32_t)(ks * BS * 16)));
+        fp8x4_to_f16x2x2<KV>(w, b0, b1);
         const uint32_t a1 = (RS == 2) ? qa[ks][2] : 0u, a3 = (RS == 2) ? qa[ks][3] : 0u;
         MmaOp<MT>::run(s[nt], qa[ks][0], a1, qa[ks][1], a3, b0, b1);
       }
@@ -168,7 +204,7 @@ __device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
     for (int nt = 0; nt < NT; ++nt) {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        const int t = nt * 8 + q4 * 2 + e;  // token within page
+        const int t = page_token<KV, BS>(nt, q4, e);  // token within page
         float x = s[nt][2 * rs + e] * scale_log2 + slope[rs] * (tok_rel0 + (float)t);
         if (TAIL && t >= valid) x = kNegInf;
         if (!row_on[rs]) x = kNegInf;
@@ -212,7 +248,7 @@ __device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
   if constexpr (TAIL) {
 #pragma unroll
     for (int h = 0; h < (BS >= 16 ? BS / 8 : 1); ++h) {
-      const int t0 = h * 8 + q4 * 2;
+      const int t0 = page_token<KV, BS>(h, q4, 0);
       vmask[h] = (t0 < valid ? 0x0000ffffu : 0u) | (t0 + 1 < valid ? 0xffff0000u : 0u);
     }
   }
@@ -281,26 +317,43 @@ __device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
         }
       }
     } else {
-      // fp8 V page [D][BS] bytes.  Lane (n = lane/4 -> d = 8j + n, q4) needs tokens (2q4, 2q4+1) and
-      // (8 + 2q4, 9 + 2q4) of the k-step: two 16-bit shared loads.
-      const uint32_t base = v_smem + (uint32_t)((lane >> 2) * BS + q4 * 2 + kk * 16);
+      if constexpr (BS >= 16) {
+        // fp8 V page [D][BS] bytes.  Lane (n = lane/4 -> d = 8j + n, q4) needs the tokens of its
+        // two P fragments = 4*q4..4*q4+3 of this 16-token group (see page_token): one 32-bit load.
+        // For q4 >= 2 tile 2kk holds the upper token pair, so the halves are swapped first.
+        const uint32_t base = v_smem + (uint32_t)((lane >> 2) * BS + q4 * 4 + kk * 16);
+        const uint32_t rot = (q4 & 2) ? 16u : 0u;
 #pragma unroll
-      for (int j = 0; j < NDT; ++j) {
-        uint16_t w0, w1 = 0;
-        asm volatile("ld.shared.u16 %0, [%1];" : "=h"(w0) : "r"(base + (uint32_t)(j * 8 * BS)));
-        if constexpr (BS >= 16)
-          asm volatile("ld.shared.u16 %0, [%1];" : "=h"(w1) : "r"(base + (uint32_t)(j * 8 * BS + 8)));
-        uint32_t b0 = fp8x2_to_f16x2<KV>(w0);
-        uint32_t b1 = (BS >= 16) ? fp8x2_to_f16x2<KV>(w1) : 0u;
-        if constexpr (TAIL) {
-          b0 &= vmask[BS >= 16 ? 2 * kk : 0];
-          if constexpr (BS >= 16) b1 &= vmask[2 * kk + 1];
+        for (int j = 0; j < NDT; ++j) {
+          uint32_t w, b0, b1;
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(base + (uint32_t)(j * 8 * BS)));
+          w = __funnelshift_l(w, w, rot);
+          fp8x4_to_f16x2x2<KV>(w, b0, b1);
+          if constexpr (TAIL) {
+            b0 &= vmask[2 * kk];
+            b1 &= vmask[2 * kk + 1];
+          }
+          float acc[4] = {o[j][0], o[j][1], RS == 2 ? o[j][2 * (RS - 1)] : 0.f,
+                          RS == 2 ? o[j][2 * (RS - 1) + 1] : 0.f};
+          MmaOp<MT>::run(acc, pa0, pa1, pa2, pa3, b0, b1);
+          o[j][0] = acc[0]; o[j][1] = acc[1];
+          if constexpr (RS == 2) { o[j][2] = acc[2]; o[j][3] = acc[3]; }
         }
-        float acc[4] = {o[j][0], o[j][1], RS == 2 ? o[j][2 * (RS - 1)] : 0.f,
-                        RS == 2 ? o[j][2 * (RS - 1) + 1] : 0.f};
-        MmaOp<MT>::run(acc, pa0, pa1, pa2, pa3, b0, b1);
-        o[j][0] = acc[0]; o[j][1] = acc[1];
-        if constexpr (RS == 2) { o[j][2] = acc[2]; o[j][3] = acc[3]; }
+      } else {
+        // 8-token fp8 pages: tokens (2q4, 2q4+1) of row d = 8j + n; upper half of the k-step is zero
+        const uint32_t base = v_smem + (uint32_t)((lane >> 2) * BS + q4 * 2);
+#pragma unroll
+        for (int j = 0; j < NDT; ++j) {
+          uint16_t w0;
+          asm volatile("ld.shared.u16 %0, [%1];" : "=h"(w0) : "r"(base + (uint32_t)(j * 8 * BS)));
+          uint32_t b0 = fp8x2_to_f16x2<KV>(w0);
+          if constexpr (TAIL) b0 &= vmask[0];
+          float acc[4] = {o[j][0], o[j][1], RS == 2 ? o[j][2 * (RS - 1)] : 0.f,
+                          RS == 2 ? o[j][2 * (RS - 1) + 1] : 0.f};
+          MmaOp<MT>::run(acc, pa0, pa1, pa2, pa3, b0, 0u);
+          o[j][0] = acc[0]; o[j][1] = acc[1];
+          if constexpr (RS == 2) { o[j][2] = acc[2]; o[j][3] = acc[3]; }
+        }
       }
     }
   }

@@ -20,7 +20,12 @@ constexpr int kPartitionSize = 512;  // fixed by the op contract (paged_attn.py:
 
 // ---------------------------------------------------------------------------------------
 // v2 merge: out = sum_j tmp_out_j * exp_sum_j * e^(m_j - m) / (sum_j exp_sum_j e^(m_j - m) + 1e-6)
-// One warp per (seq, head); 4 (seq, head) pairs per CTA.  (Reference: one 128-thread CTA per pair.)
+// (reference: paged_attention_v2_reduce_kernel, attention_kernels.cu:565-669, one 128-thread CTA
+// per (seq, head)).  Here: one warp per (seq, head), 4 pairs per CTA; the lanes first turn the
+// partition statistics into normalised weights held in shared memory, then stream tmp_out with
+// 4-byte loads, partitions outermost so every load is one coalesced row.
+// `partition_tokens` is the context length one partition covers (a multiple of 512 chosen by
+// make_plan; the scratch tensors' partition stride stays max_num_partitions).
 // ---------------------------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(128)
@@ -28,13 +33,15 @@ paged_attention_v2_reduce_kernel(T* __restrict__ out, const float* __restrict__ 
                                  const float* __restrict__ max_logits,
                                  const T* __restrict__ tmp_out, const int32_t* __restrict__ seq_lens,
                                  int num_heads, int head_size, int max_num_partitions,
-                                 int64_t total_pairs) {
+                                 int partition_tokens, int weights_stride, int64_t total_pairs) {
+  extern __shared__ float wsm[];  // [4 warps][weights_stride]
   const int lane = threadIdx.x & 31;
-  const int64_t pair = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int warp = threadIdx.x >> 5;
+  const int64_t pair = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
   if (pair >= total_pairs) return;
   const int seq = (int)(pair / num_heads);
   const int seq_len = seq_lens[seq];
-  const int np = (seq_len + kPartitionSize - 1) / kPartitionSize;
+  const int np = (seq_len + partition_tokens - 1) / partition_tokens;
   T* o = out + pair * head_size;
   const T* t = tmp_out + pair * max_num_partitions * head_size;
   if (np <= 1) {
@@ -45,20 +52,30 @@ paged_attention_v2_reduce_kernel(T* __restrict__ out, const float* __restrict__ 
   }
   const float* ml = max_logits + pair * max_num_partitions;
   const float* es = exp_sums + pair * max_num_partitions;
+  float* w = wsm + warp * weights_stride;
   float mx = -__builtin_huge_valf();
   for (int j = lane; j < np; j += 32) mx = fmaxf(mx, ml[j]);
 #pragma unroll
   for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
   float sum = 0.f;
-  for (int j = lane; j < np; j += 32) sum += es[j] * expf(ml[j] - mx);
+  for (int j = lane; j < np; j += 32) {
+    const float r = es[j] * expf(ml[j] - mx);
+    w[j] = r;
+    sum += r;
+  }
 #pragma unroll
   for (int s = 16; s >= 1; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
   const float inv = __fdividef(1.f, sum + 1e-6f);
-  for (int d = lane; d < head_size; d += 32) {
-    float acc = 0.f;
-    for (int j = 0; j < np; ++j)
-      acc += to_f32<T>(t[(int64_t)j * head_size + d]) * (es[j] * expf(ml[j] - mx)) * inv;
-    o[d] = from_f32<T>(acc);
+  __syncwarp();
+  for (int d0 = 2 * lane; d0 < head_size; d0 += 64) {  // head sizes are even
+    float a0 = 0.f, a1 = 0.f;
+    for (int j = 0; j < np; ++j) {
+      const float wj = w[j] * inv;
+      a0 += to_f32<T>(t[(int64_t)j * head_size + d0]) * wj;
+      a1 += to_f32<T>(t[(int64_t)j * head_size + d0 + 1]) * wj;
+    }
+    o[d0] = from_f32<T>(a0);
+    o[d0 + 1] = from_f32<T>(a1);
   }
 }
 
@@ -86,6 +103,8 @@ static Knobs& knobs() {
 struct Plan {
   AttnEntry entry;
   int grows, gchunks, nwarps, nstages, cluster, ctas_per_sm, num_sms;
+  int v2_parts;             // v2: partitions per sequence at max_seq_len (1 = single pass)
+  int v2_partition_tokens;  // v2: context tokens per partition (multiple of 512)
   size_t smem;
 };
 
@@ -131,18 +150,36 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
   cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device);
   pl.num_sms = num_sms;
 
-  // Pipeline geometry: aim for two resident CTAs per SM and >= 96 KiB of pages in flight per SM.
+  // Pipeline geometry.  Registers allow three 4-warp CTAs per SM (<= 168 regs x 128 threads), and
+  // three CTAs with a short ring beat two with a deep one on every measured config
+  // (profiles/r1_sweep_grid.md): size the per-warp ring so that three CTAs fit in 227 KiB of
+  // shared memory, between 2 and 4 stages (one stage = one K page + one V page).
   const int es = kv_dtype == B200_KV_AUTO ? 2 : 1;
   const size_t stage_bytes = (size_t)2 * head_size * block_size * es;
   pl.nwarps = knobs().warps.load();
   if (pl.nwarps < 1) pl.nwarps = 4;
   if (pl.nwarps > 8) pl.nwarps = 8;
+  const long long base = (long long)num_seqs * num_kv_heads * pl.gchunks;  // CTAs before any split
   int ns = knobs().stages.load();
   if (ns <= 0) {
-    const size_t budget = 104 * 1024;  // per CTA, so that two CTAs fit in 227 KiB
-    ns = (int)(budget / ((size_t)pl.nwarps * stage_bytes));
-    if (ns > 8) ns = 8;
-    if (ns < 2) ns = 2;
+    // candidate A: ring that lets three CTAs share an SM (2..4 stages); candidate B: a deeper ring
+    // with two CTAs per SM.  A wins whenever the grid runs for many waves or fits in one; B wins
+    // when a 1-3 wave grid would leave A with a nearly empty last wave (c2: 512 CTAs on 444 slots).
+    auto fit = [&](size_t budget, int cap) {
+      int n = (int)(budget / ((size_t)pl.nwarps * stage_bytes));
+      return n > cap ? cap : (n < 2 ? 2 : n);
+    };
+    const int ns_a = fit((size_t)74 * 1024, 4), ns_b = fit((size_t)104 * 1024, 6);
+    ns = ns_a;
+    if (ns_b > ns_a) {
+      const long long slots_a = (long long)num_sms * 3, slots_b = (long long)num_sms * 2;
+      const long long waves_a = (base + slots_a - 1) / slots_a, waves_b = (base + slots_b - 1) / slots_b;
+      if (waves_a >= 2 && waves_a <= 3) {
+        const double eff_a = (double)base / (double)(waves_a * slots_a);
+        const double eff_b = (double)base / (double)(waves_b * slots_b);
+        if (eff_b > eff_a + 0.1) ns = ns_b;
+      }
+    }
   }
   if (ns > 32) ns = 32;
   while (ns > 1 && e.smem(pl.nwarps, ns) > (size_t)227 * 1024) --ns;
@@ -153,8 +190,12 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
   pl.ctas_per_sm = e.occupancy(pl.nwarps, ns);
   if (pl.ctas_per_sm < 1) pl.ctas_per_sm = 1;
 
-  // v1 context split = cluster size.  Pick the split that fills whole waves of the machine while
-  // leaving every CTA at least 2 pages per warp.
+  // v1 context split = cluster size.  Measured on B200 (profiles/r1_sweep_c2.md): an unsplit grid
+  // of >= one CTA per residency slot already reaches ~97 % of the HBM peak (partial waves do not
+  // matter for a bandwidth-bound kernel), while clusters cost co-scheduling and the DSMEM merge.
+  // So split only when the grid cannot fill the machine: the smallest power of two that gives at
+  // least half the residency slots (= every SM) a CTA, leaving every warp at least 2 pages
+  // (profiles/r1_sweep_grid.md: B=16 -> 2, B=32 -> 1, B<=4 -> 8 are the measured optima).
   pl.cluster = 1;
   if (version == 1) {
     const int forced = knobs().cluster.load();
@@ -162,21 +203,32 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
       pl.cluster = forced;
     } else {
       const long long slots = (long long)num_sms * pl.ctas_per_sm;
-      const long long base = (long long)num_seqs * num_kv_heads * pl.gchunks;
       const int max_pages = (max_seq_len + block_size - 1) / block_size;
-      double best = -1.0;
-      for (int s = 1; s <= 8; s *= 2) {
-        if (s > 1 && max_pages / s < 2 * pl.nwarps) break;
-        const long long n = base * s;
-        const long long waves = (n + slots - 1) / slots;
-        double eff = (double)n / (double)(waves * slots);
-        eff -= 0.01 * (s > 1 ? 1 : 0) + 0.002 * s;  // merging is not free: prefer smaller splits
-        if (eff > best + 1e-9) {
-          best = eff;
-          pl.cluster = s;
-        }
-      }
+      int s = 1;
+      while (s < 8 && 2 * base * s < slots && max_pages / (2 * s) >= 2 * pl.nwarps) s *= 2;
+      pl.cluster = s;
     }
+  }
+  // v2 context split through the caller's scratch.  The op contract fixes the scratch shape
+  // ([B,H,ceil(max_seq_len/512)(,D)]) but its contents are scratch (never read by the caller,
+  // paged_attn.py:156-191), so the partition length is a multiple m of 512 tokens chosen like the
+  // v1 split: as few, as long partitions as still give every residency slot about two CTAs.
+  // m = 1 reproduces the reference's geometry; when one partition covers max_seq_len the kernel
+  // writes `out` directly and the merge launch is skipped.
+  pl.v2_parts = 1;
+  pl.v2_partition_tokens = kPartitionSize;
+  if (version == 2) {
+    const int p512 = max_seq_len > 0 ? (max_seq_len + kPartitionSize - 1) / kPartitionSize : 1;
+    const long long slots = (long long)num_sms * pl.ctas_per_sm;
+    long long want = (2 * slots + base - 1) / base;  // partitions per sequence we would like
+    if (want < 1) want = 1;
+    if (want > p512) want = p512;
+    int m = (int)(p512 / want);
+    if (m < 1) m = 1;
+    const int forced = knobs().cluster.load();  // tuning: "cluster" knob = forced m for v2
+    if (forced > 0) m = forced;
+    pl.v2_partition_tokens = kPartitionSize * m;
+    pl.v2_parts = (p512 + m - 1) / m;
   }
   return B200_OK;
 }
@@ -237,7 +289,8 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
   p.gchunks = pl.gchunks;
   p.max_blocks_per_seq = max_num_blocks_per_seq;
   p.max_num_partitions = max_num_partitions;
-  p.partition_pages = version == 2 ? kPartitionSize / block_size : 0;
+  const bool split_v2 = version == 2 && pl.v2_parts > 1;
+  p.partition_pages = split_v2 ? pl.v2_partition_tokens / block_size : 0;
   p.num_stages = pl.nstages;
   p.q_stride = q_stride;
   p.kv_block_stride = kv_block_stride;
@@ -255,25 +308,28 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
     p.bs_head_sliding_step = bsp->head_sliding_step;
   }
 
-  const int splits = version == 2 ? max_num_partitions : pl.cluster;
+  const int splits = version == 2 ? pl.v2_parts : pl.cluster;
   B200_CHECK_ARG((long long)num_kv_heads * pl.gchunks <= 65535 && num_seqs <= 65535,
                  "paged_attention: grid too large");
   dim3 grid(splits, num_kv_heads * pl.gchunks, num_seqs);
   rc = pl.entry.launch(p, grid, version == 2 ? 1 : pl.cluster, pl.nwarps, pl.nstages, dev, stream);
   if (rc != B200_OK) return rc;
 
-  if (version == 2) {
+  if (split_v2) {
     const int64_t pairs = (int64_t)num_seqs * num_heads;
     const unsigned blocks = (unsigned)((pairs + 3) / 4);
+    const int wstride = (pl.v2_parts + 3) & ~3;
+    const size_t wsmem = (size_t)4 * wstride * sizeof(float);
     if (q_dtype == B200_DT_F16)
-      paged_attention_v2_reduce_kernel<__half><<<blocks, 128, 0, stream>>>(
+      paged_attention_v2_reduce_kernel<__half><<<blocks, 128, wsmem, stream>>>(
           static_cast<__half*>(out), exp_sums, max_logits, static_cast<const __half*>(tmp_out),
-          seq_lens, num_heads, head_size, max_num_partitions, pairs);
+          seq_lens, num_heads, head_size, max_num_partitions, pl.v2_partition_tokens, wstride,
+          pairs);
     else
-      paged_attention_v2_reduce_kernel<__nv_bfloat16><<<blocks, 128, 0, stream>>>(
+      paged_attention_v2_reduce_kernel<__nv_bfloat16><<<blocks, 128, wsmem, stream>>>(
           static_cast<__nv_bfloat16*>(out), exp_sums, max_logits,
           static_cast<const __nv_bfloat16*>(tmp_out), seq_lens, num_heads, head_size,
-          max_num_partitions, pairs);
+          max_num_partitions, pl.v2_partition_tokens, wstride, pairs);
     count_launch();
     B200_CUDA_OK(cudaGetLastError());
   }
@@ -339,7 +395,7 @@ extern "C" int b200_paged_attention_plan(int version, int num_seqs, int num_head
   plan->num_stages = pl.nstages;
   plan->smem_bytes = (int32_t)pl.smem;
   plan->ctas_per_sm = pl.ctas_per_sm;
-  plan->grid_x = version == 2 ? (max_seq_len + kPartitionSize - 1) / kPartitionSize : pl.cluster;
+  plan->grid_x = version == 2 ? pl.v2_parts : pl.cluster;
   plan->grid_y = num_kv_heads * pl.gchunks;
   plan->grid_z = num_seqs;
   return B200_OK;

@@ -124,3 +124,49 @@ def test_unsupported_raises(ops):
     bad = dict(g, block_size=24)
     with pytest.raises(RuntimeError, match="block size"):
         ops.paged_attention_v1(out, *attn_args(bad))
+
+
+def make_fp8_case(oracle, lens, H, KH, D, BS, dtype, kv, k_scale, v_scale, seed):
+    """Quantise a 16-bit case's caches with the oracle's (pinned, bit-exact) fp8 codec."""
+    c = make_case(len(lens), H, KH, D, BS, lens, dtype, seed=seed, cache_dtype=dtype)
+    x = 16
+    kc16 = c["key_cache"]                       # [nb, KH, D/x16, BS, x16] with x16 = 8
+    nb = kc16.shape[0]
+    # re-tile K to the fp8 layout (x = 16 elements per 16-byte chunk)
+    k_logical = kc16.permute(0, 1, 3, 2, 4).reshape(nb, KH, BS, D)          # [nb, KH, BS, D]
+    k8_src = k_logical.view(nb, KH, BS, D // x, x).permute(0, 1, 3, 2, 4).contiguous()
+    kc8 = torch.empty(k8_src.shape, dtype=torch.uint8)
+    vc8 = torch.empty(c["value_cache"].shape, dtype=torch.uint8)
+    oracle.convert_fp8(kc8, k8_src, k_scale, kv)
+    oracle.convert_fp8(vc8, c["value_cache"].contiguous(), v_scale, kv)
+    c["key_cache"], c["value_cache"] = kc8, vc8
+    return c
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("kv", ["fp8", "fp8_e5m2"])
+@pytest.mark.parametrize("version", [1, 2])
+def test_fp8_kv_cache(ops, oracle, dtype, kv, version):
+    lens = [1, 9, 16, 31, 500, 513, 1100]
+    for (H, KH, ks, vs) in ((28, 4, 0.05, 0.02), (8, 8, 1.0, 1.0), (32, 2, 0.3, 2.0)):
+        c = make_fp8_case(oracle, lens, H, KH, 128, 16, dtype, kv, ks, vs, seed=H)
+        check(ops, oracle, c, dtype, version, kv=kv, ks=ks, vs=vs)
+
+
+def test_fp8_vs_reference_cuda_kernels(ops, oracle):
+    from oracle import ref
+    if not ref.have_ref_cuda():
+        pytest.skip("oracle/_ref/libref_cuda.so not built")
+    rC, _ = ref.ref_cuda()
+    lens = [3, 700, 2048, 1023, 64]
+    for dtype in (torch.float16, torch.bfloat16):
+        for kv in ("fp8", "fp8_e5m2"):
+            c = make_fp8_case(oracle, lens, 28, 4, 128, 16, dtype, kv, 0.05, 0.03, seed=21)
+            g = to_device(c, "cuda")
+            for version in (1, 2):
+                run = run_v1 if version == 1 else run_v2
+                got = run(ops, g, kv=kv, ks=0.05, vs=0.03)
+                want = run(rC, g, kv=kv, ks=0.05, vs=0.03)
+                torch.cuda.synchronize()
+                err = (got.float() - want.float()).abs().max().item()
+                assert err <= TOL[dtype], f"{kv} v{version} {dtype}: max-abs {err} vs reference CUDA"
