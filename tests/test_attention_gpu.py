@@ -170,3 +170,65 @@ def test_fp8_vs_reference_cuda_kernels(ops, oracle):
                 torch.cuda.synchronize()
                 err = (got.float() - want.float()).abs().max().item()
                 assert err <= TOL[dtype], f"{kv} v{version} {dtype}: max-abs {err} vs reference CUDA"
+
+
+HEADS = [64, 80, 96, 112, 120, 128, 192, 256]   # attention_kernels.cu:738-769
+BLOCKS = [8, 16, 32]                             # attention_kernels.cu:792-806
+
+
+@pytest.mark.parametrize("head_size", HEADS)
+@pytest.mark.parametrize("block_size", BLOCKS)
+def test_dispatch_surface_auto(ops, oracle, head_size, block_size):
+    lens = [1, block_size, block_size + 1, 257, 600]
+    for dtype, (H, KH) in ((torch.float16, (8, 2)), (torch.bfloat16, (12, 1))):
+        c = make_case(len(lens), H, KH, head_size, block_size, lens, dtype, seed=head_size + block_size,
+                      nan_padding=True)
+        for version in (1, 2):
+            check(ops, oracle, c, dtype, version)
+
+
+@pytest.mark.parametrize("head_size", [64, 80, 96, 112, 128, 192, 256])
+@pytest.mark.parametrize("block_size", BLOCKS)
+def test_dispatch_surface_fp8(ops, oracle, head_size, block_size):
+    lens = [1, block_size + 3, 300, 520]
+    for dtype, kv, (H, KH) in ((torch.float16, "fp8", (8, 2)), (torch.bfloat16, "fp8_e5m2", (16, 1))):
+        c = make_fp8_case(oracle, lens, H, KH, head_size, block_size, dtype, kv, 0.1, 0.2,
+                          seed=head_size * 3 + block_size)
+        for version in (1, 2):
+            check(ops, oracle, c, dtype, version, kv=kv, ks=0.1, vs=0.2)
+
+
+@pytest.mark.parametrize("tail", [(0, 2, 4, 64, 1), (1, 1, 3, 32, -1), (0, 16, 8, 16, 0), (0, 0, 2, 64, 3)])
+def test_blocksparse(ops, oracle, tail):
+    # tail = (tp_rank, local_blocks, vert_stride, blocksparse_block_size, head_sliding_step)
+    lens = [70, 640, 1500, 129]
+    c = make_case(len(lens), 16, 4, 128, 16, lens, torch.float16, seed=31)
+    for version in (1, 2):
+        check(ops, oracle, c, torch.float16, version, tail=tail)
+    from oracle import ref
+    if ref.have_ref_cuda():
+        rC, _ = ref.ref_cuda()
+        g = to_device(c, "cuda")
+        for version in (1, 2):
+            run = run_v1 if version == 1 else run_v2
+            got, want = run(ops, g, tail=tail), run(rC, g, tail=tail)
+            torch.cuda.synchronize()
+            assert (got.float() - want.float()).abs().max().item() <= TOL[torch.float16]
+
+
+def test_dispatch_vs_reference_cuda(ops):
+    """Every (head size, block size) against the reference CUDA kernels, fp16 'auto'."""
+    from oracle import ref
+    if not ref.have_ref_cuda():
+        pytest.skip("oracle/_ref/libref_cuda.so not built")
+    rC, _ = ref.ref_cuda()
+    for D in HEADS:
+        for BS in BLOCKS:
+            lens = [5, 1000, 513]
+            g = to_device(make_case(len(lens), 8, 2, D, BS, lens, torch.float16, seed=D + BS), "cuda")
+            for version in (1, 2):
+                run = run_v1 if version == 1 else run_v2
+                got, want = run(ops, g), run(rC, g)
+                torch.cuda.synchronize()
+                err = (got.float() - want.float()).abs().max().item()
+                assert err <= 2e-3, f"D={D} BS={BS} v{version}: {err}"
