@@ -90,7 +90,6 @@ def test_prefill_then_decode_steps(dtype, kv, tol):
             want = ref_attention(q[i].view(H, D).float().cpu(), hist_k[i], hist_v[i], scale)
             err = (out[i].view(H, D).double().cpu() - want).abs().max().item()
             assert err <= tol, f"step {step} seq {i}: {err}"
-    assert impl.forward(q, k, v, None, decode_meta(slots, lens, bt, dev)).shape == q.shape or True
 
 
 def test_profile_run_without_cache():
@@ -120,7 +119,7 @@ def test_cache_engine_preemption_round_trip(cache_dtype):
     g = torch.Generator().manual_seed(3)
     for t in eng.gpu_cache:
         t.view(torch.uint8).copy_(torch.randint(0, 255, t.view(torch.uint8).shape, dtype=torch.uint8, generator=g))
-    before = [t.clone() for t in eng.gpu_cache]
+    before = [t.clone().view(torch.uint8) for t in eng.gpu_cache]
     victim = [5, 17, 2, 9]
     out_map = torch.tensor([[b, i] for i, b in enumerate(victim)], dtype=torch.int64)
     eng.apply(blocks_to_swap_out=out_map.pin_memory())
@@ -131,15 +130,17 @@ def test_cache_engine_preemption_round_trip(cache_dtype):
         t[:, new_home] = 0
     eng.apply(blocks_to_swap_in=in_map)
     torch.cuda.synchronize()
+    gpu = [t.view(torch.uint8) for t in eng.gpu_cache]   # compare bytes (random bits include NaNs)
+    cpu = [t.view(torch.uint8) for t in eng.cpu_cache]
     for layer in range(L):
         for kvi in range(2):
             for old, new in zip(victim, new_home):
-                assert torch.equal(eng.gpu_cache[layer][kvi, new], before[layer][kvi, old])
-            assert torch.equal(eng.gpu_cache[layer][kvi, 20], before[layer][kvi, 9])
-            assert torch.equal(eng.gpu_cache[layer][kvi, 21], before[layer][kvi, 9])
-            assert torch.equal(eng.cpu_cache[layer][kvi, 1], before[layer][kvi, 17].cpu())
+                assert torch.equal(gpu[layer][kvi, new], before[layer][kvi, old])
+            assert torch.equal(gpu[layer][kvi, 20], before[layer][kvi, 9])
+            assert torch.equal(gpu[layer][kvi, 21], before[layer][kvi, 9])
+            assert torch.equal(cpu[layer][kvi, 1], before[layer][kvi, 17].cpu())
             untouched = [b for b in range(24) if b not in new_home + [20, 21]]
-            assert torch.equal(eng.gpu_cache[layer][kvi, untouched], before[layer][kvi, untouched])
+            assert torch.equal(gpu[layer][kvi, untouched], before[layer][kvi, untouched])
 
 
 def test_forward_decode_v2_path_and_scratch_reuse():
