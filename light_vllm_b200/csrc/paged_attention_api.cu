@@ -15,6 +15,8 @@ AttnEntry attn_lookup_f16_e5m2(int, int, int);
 AttnEntry attn_lookup_bf16_auto(int, int, int);
 AttnEntry attn_lookup_bf16_e4m3(int, int, int);
 AttnEntry attn_lookup_bf16_e5m2(int, int, int);
+AttnEntry attn_lookup_f32(int head_size, int block_size, int kv_dtype, int group_rows);
+int attn_f32_group_rows(int group, int head_size);
 
 constexpr int kPartitionSize = 512;  // fixed by the op contract (paged_attn.py:14)
 
@@ -128,9 +130,13 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
         : kv_dtype == B200_KV_FP8_E4M3 ? attn_lookup_bf16_e4m3(head_size, block_size, pl.grows)
         : kv_dtype == B200_KV_FP8_E5M2 ? attn_lookup_bf16_e5m2(head_size, block_size, pl.grows)
                                        : e;
+  } else if (q_dtype == B200_DT_F32) {
+    // fp32 queries run on the CUDA-core kernel (paged_attention_f32.cu): 1, 2 or 4 q-heads per CTA
+    pl.grows = attn_f32_group_rows(group, head_size);
+    pl.gchunks = (group + pl.grows - 1) / pl.grows;
+    e = attn_lookup_f32(head_size, block_size, kv_dtype, pl.grows);
   } else {
-    set_error("Unsupported data type: query dtype %d (float32 queries are not instantiated yet)",
-              q_dtype);
+    set_error("Unsupported data type: query dtype %d", q_dtype);
     return B200_ERR_UNSUPPORTED;
   }
   if (kv_dtype < 0 || kv_dtype > B200_KV_FP8_E5M2) {
@@ -154,11 +160,15 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
   // three CTAs with a short ring beat two with a deep one on every measured config
   // (profiles/r1_sweep_grid.md): size the per-warp ring so that three CTAs fit in 227 KiB of
   // shared memory, between 2 and 4 stages (one stage = one K page + one V page).
-  const int es = kv_dtype == B200_KV_AUTO ? 2 : 1;
+  const int es = kv_dtype == B200_KV_AUTO ? (q_dtype == B200_DT_F32 ? 4 : 2) : 1;
   const size_t stage_bytes = (size_t)2 * head_size * block_size * es;
   pl.nwarps = knobs().warps.load();
   if (pl.nwarps < 1) pl.nwarps = 4;
   if (pl.nwarps > 8) pl.nwarps = 8;
+  if (q_dtype == B200_DT_F32) {  // 128-thread kernel; fp32 pages are up to 32 KiB each
+    if (pl.nwarps > 4) pl.nwarps = 4;
+    while (pl.nwarps > 1 && (size_t)pl.nwarps * 2 * stage_bytes > (size_t)200 * 1024) pl.nwarps /= 2;
+  }
   const long long base = (long long)num_seqs * num_kv_heads * pl.gchunks;  // CTAs before any split
   int ns = knobs().stages.load();
   if (ns <= 0) {
@@ -199,7 +209,9 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
   pl.cluster = 1;
   if (version == 1) {
     const int forced = knobs().cluster.load();
-    if (forced > 0) {
+    if (q_dtype == B200_DT_F32) {
+      pl.cluster = 1;  // the fp32 kernel has no cluster merge: v1 runs unsplit
+    } else if (forced > 0) {
       pl.cluster = forced;
     } else {
       const long long slots = (long long)num_sms * pl.ctas_per_sm;
@@ -255,7 +267,7 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
                      max_seq_len, q_dtype, kv_dtype, dev);
   if (rc != B200_OK) return rc;
 
-  const int es = kv_dtype == B200_KV_AUTO ? 2 : 1;
+  const int es = kv_dtype == B200_KV_AUTO ? (q_dtype == B200_DT_F32 ? 4 : 2) : 1;
   B200_CHECK_ARG((reinterpret_cast<uintptr_t>(key_cache) & 15) == 0 &&
                      (reinterpret_cast<uintptr_t>(value_cache) & 15) == 0 &&
                      (kv_block_stride * es) % 16 == 0 && (kv_head_stride * es) % 16 == 0,
@@ -323,6 +335,11 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
     if (q_dtype == B200_DT_F16)
       paged_attention_v2_reduce_kernel<__half><<<blocks, 128, wsmem, stream>>>(
           static_cast<__half*>(out), exp_sums, max_logits, static_cast<const __half*>(tmp_out),
+          seq_lens, num_heads, head_size, max_num_partitions, pl.v2_partition_tokens, wstride,
+          pairs);
+    else if (q_dtype == B200_DT_F32)
+      paged_attention_v2_reduce_kernel<float><<<blocks, 128, wsmem, stream>>>(
+          static_cast<float*>(out), exp_sums, max_logits, static_cast<const float*>(tmp_out),
           seq_lens, num_heads, head_size, max_num_partitions, pl.v2_partition_tokens, wstride,
           pairs);
     else
