@@ -39,6 +39,12 @@ CONFIGS = {
                label="Llama-3-8B-shaped decode bf16, batch 256, ctx 4096, paged_attention_v2"),
     "c4": dict(dtype="bfloat16", kv="fp8", H=28, KH=4, D=128, BS=16, B=512, ctx=8192, version=1,
                label="fp8_e4m3 KV cache Qwen2-7B-shaped decode, batch 512, ctx 8192"),
+    # configs[4]: per GPU 16 sequences x 128 Ki tokens (512 MiB of KV per sequence per layer pool);
+    # --ctx 32768|65536|131072 and --batch rescale it; sequences are sharded over the ranks.
+    "c5": dict(dtype="bfloat16", kv="auto", H=32, KH=8, D=128, BS=16, B=16, ctx=131072, version=2,
+               preempt=True,
+               label="long-context decode bf16 (Llama-3-8B-shaped), 128 Ki-token sequences, "
+                     "sequence-sharded KV pools, copy_blocks/swap_blocks under preemption"),
 }
 
 
@@ -271,7 +277,10 @@ def run_b200_arm(args, c):
     scale = D ** -0.5
     k_scale = v_scale = 1.0 if kv == "auto" else 0.05
     blocks_per_seq = (ctx + BS - 1) // BS
-    NB = B * blocks_per_seq + 64
+    preempt = bool(c.get("preempt")) and not args.no_preempt
+    # 64 spare blocks; plus one whole sequence's worth past them for the preemption exercise (CoW targets)
+    n_live = B * blocks_per_seq + 64          # block ids the block tables draw from
+    NB = n_live + (blocks_per_seq if preempt else 0)
     torch.manual_seed(1234 + rank)
 
     # ---- this rank's shard: its own pools, block tables and sequences (sequence sharding) ----
@@ -287,7 +296,7 @@ def run_b200_arm(args, c):
             pool = torch.empty(shape, dtype=dtype, device=dev).uniform_(-scale, scale)
         pools.append(pool)
     split = [PagedAttention.split_kv_cache(p, KH, D) for p in pools]
-    block_tables_h = torch.randperm(NB)[:B * blocks_per_seq].view(B, blocks_per_seq).int().pin_memory()
+    block_tables_h = torch.randperm(n_live)[:B * blocks_per_seq].view(B, blocks_per_seq).int().pin_memory()
     seq_lens_h = torch.full((B,), ctx, dtype=torch.int32).pin_memory()
     slots_h = (block_tables_h[:, (ctx - 1) // BS].long() * BS + (ctx - 1) % BS).pin_memory()
     qkv_h = torch.empty(B, (H + 2 * KH) * D, dtype=dtype).uniform_(-scale, scale).pin_memory()
@@ -388,10 +397,103 @@ def run_b200_arm(args, c):
         e2e_step()
     ms_e2e = timed(e2e_step, args.steps)
 
+    pre = None
+    if preempt:
+        pre = preemption_exercise(args, c, dev, pools, block_tables_h, NB, device_step, timed)
+
     return dict(rank=rank, world=world, ms_total=ms_total, ms_e2e=ms_e2e, ms_attn=ms_attn,
-                clocks=clocks, launches=launches, h2d=h2d, d2h=d2h, L=L,
+                clocks=clocks, launches=launches, h2d=h2d, d2h=d2h, L=L, preemption=pre,
                 plan=_lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, local_rank),
                 dist=dist if world > 1 else None)
+
+
+def preemption_exercise(args, c, dev, pools, block_tables_h, NB, device_step, timed):
+    """configs[4]: what the scheduler's preemption does to one victim sequence.
+
+    swap_blocks all blocks of sequence 0 out to a pinned host pool (K and V of every layer pool),
+    scrub them on the GPU (the allocator would hand them to someone else), copy_blocks every
+    block of sequence 1 to spare blocks (a fork's copy-on-write, at scale), swap the victim back
+    in; the pools must be bit-exact afterwards.  Then the three ops are timed on their own, and
+    the decode step is timed with one such cycle every ``--preempt-every`` steps on the same
+    stream (the reference issues swap/copy before the model step, gpu_worker.py:206-221)."""
+    import torch
+    from light_vllm_b200.attention import PagedB200AttentionBackend as Backend
+    BS, KH, D, L = c["BS"], c["KH"], c["D"], len(pools)
+    bps = block_tables_h.shape[1]
+    esz = pools[0].element_size()
+    block_bytes = BS * KH * D * esz                       # one block of one layer's K (== V)
+    cpu_pools = [torch.zeros((2, bps, BS * KH * D), dtype=pools[0].dtype).pin_memory()
+                 for _ in range(L)]
+    victim = block_tables_h[0].long()
+    idx = torch.arange(bps, dtype=torch.int64)
+    out_map = torch.stack([victim, idx], dim=1).contiguous()          # gpu block -> cpu block (CPU tensor)
+    in_map = torch.stack([idx, victim], dim=1).contiguous()
+    spare = torch.arange(NB - bps, NB, dtype=torch.int64)
+    cow_map = torch.stack([block_tables_h[1].long(), spare], dim=1).contiguous().pin_memory()
+    vdev = victim.to(dev)
+
+    # ---- bit-exact round trip (untimed) ----
+    before = [p[:, vdev].clone() for p in pools[:1]] + [None] * (L - 1)   # 1 GiB: layer 0 in full
+    sums = [torch.sum(p[:, vdev].view(torch.int32), dtype=torch.int64).item() for p in pools]
+    for l in range(L):
+        Backend.swap_blocks(pools[l], cpu_pools[l], out_map)
+    for p in pools:
+        p[:, vdev] = 0
+    Backend.copy_blocks(pools, cow_map)
+    for l in range(L):
+        Backend.swap_blocks(cpu_pools[l], pools[l], in_map)
+    torch.cuda.synchronize()
+    ok = torch.equal(pools[0][:, vdev], before[0])
+    ok = ok and all(torch.sum(p[:, vdev].view(torch.int32), dtype=torch.int64).item() == s
+                    for p, s in zip(pools, sums))
+    src1 = block_tables_h[1].long().to(dev)
+    ok = ok and all(torch.equal(p[:, src1], p[:, spare.to(dev)]) for p in pools)
+    del before
+    assert ok, "preemption round trip is not bit-exact"
+
+    # ---- the three ops on their own ----
+    def swap_out():
+        for l in range(L):
+            Backend.swap_blocks(pools[l], cpu_pools[l], out_map)
+
+    def swap_in():
+        for l in range(L):
+            Backend.swap_blocks(cpu_pools[l], pools[l], in_map)
+
+    def cow():
+        Backend.copy_blocks(pools, cow_map)
+
+    reps = 3
+    for f in (swap_out, swap_in, cow):
+        f()
+    ms_out = timed(swap_out, reps) / reps
+    ms_in = timed(swap_in, reps) / reps
+    ms_cow = timed(cow, reps) / reps
+    moved = L * 2 * bps * block_bytes                      # bytes one direction, K and V
+    k = max(1, args.preempt_every)
+    state = [0]
+
+    def step_under_preemption():
+        if state[0] % k == 0:
+            swap_out()
+            cow()
+            swap_in()
+        state[0] += 1
+        device_step()
+
+    step_under_preemption()
+    state[0] = 0
+    ms_mixed = timed(step_under_preemption, args.steps) / args.steps
+    return dict(bit_exact=bool(ok), blocks=int(bps), layer_pools=L, bytes_per_direction=int(moved),
+                swap_out_GBps=round(moved / ms_out / 1e6, 2), swap_in_GBps=round(moved / ms_in / 1e6, 2),
+                swap_out_ms=round(ms_out, 3), swap_in_ms=round(ms_in, 3),
+                copy_blocks_GBps=round(2 * moved / ms_cow / 1e6, 1), copy_blocks_ms=round(ms_cow, 3),
+                copy_pairs=int(bps), preempt_every=k,
+                ms_per_step_under_preemption=round(ms_mixed, 4),
+                decode_tokens_per_s_per_layer_under_preemption=round(c["B"] * L / (ms_mixed / 1e3), 1),
+                note="swap = whole victim sequence, all layer pools, K+V, pinned host pool; copy = "
+                     "read+write bytes of a whole-sequence copy-on-write; 'under preemption' = one "
+                     "swap-out + CoW + swap-in cycle every preempt_every decode steps, same stream")
 
 
 def main():
@@ -405,8 +507,19 @@ def main():
                     help="KV pools cycled per step (each > L2; a model's layers)")
     ap.add_argument("--cpu-budget", type=float, default=12.0,
                     help="seconds of CPU work for the cpu_baseline leg (0 disables)")
+    ap.add_argument("--ctx", type=int, default=0, help="override the context length (c5: 32768..131072)")
+    ap.add_argument("--batch", type=int, default=0, help="override sequences per GPU")
+    ap.add_argument("--preempt-every", type=int, default=8,
+                    help="c5: decode steps between preemption cycles in the mixed measurement")
+    ap.add_argument("--no-preempt", action="store_true", help="c5: skip the preemption exercise")
     args = ap.parse_args()
-    c = CONFIGS[args.config]
+    c = dict(CONFIGS[args.config])
+    if args.ctx:
+        c["ctx"] = args.ctx
+    if args.batch:
+        c["B"] = args.batch
+    if args.ctx or args.batch:
+        c["label"] += f" [ctx {c['ctx']}, batch {c['B']} per GPU]"
     if args.impl == "reference":
         run_reference_arm(args, c)
         return
@@ -453,6 +566,8 @@ def main():
                          "frac_of_8TBps_datasheet": round(achieved / 8000.0, 4)},
             "clocks": r["clocks"], "gpu_launches": r["launches"],
         }
+        if r.get("preemption") is not None:
+            line["preemption"] = r["preemption"]
         if cpu is not None and "error" not in cpu:
             gbs = cpu["kv_bytes"] / cpu["best_s"] / 1e9
             line["cpu_baseline"] = {
