@@ -85,6 +85,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       : "memory");
 }
 
+// One lane of the (converged) warp: elect.sync lets ptxas move the leader's operands to uniform
+// registers once instead of looping over "active lanes" around every UBLKCP.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- 1-D bulk async copy global -> shared (TMA engine, SASS UBLKCP) ----
 __device__ __forceinline__ uint64_t l2_policy_evict_first() {
   uint64_t pol;

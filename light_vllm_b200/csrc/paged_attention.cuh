@@ -123,7 +123,8 @@ __device__ __forceinline__ int page_token(int nt, int qq, int e) {
 }
 
 // One KV page (BS tokens) against the warp's q-group: S = QK^T, online softmax, O += P V.
-template <typename T, int D, int BS, int KV, int GROWS, bool TAIL>
+// PLAIN: no ALiBi and no blocksparse mask (the common case) -- the logit is just s * scale.
+template <typename T, int D, int BS, int KV, int GROWS, bool TAIL, bool PLAIN>
 __device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
                                              const uint32_t (&qa)[(D + 15) / 16][GROWS / 4],
                                              float (&o)[D / 8][GROWS / 4], float (&m)[GROWS / 8],
@@ -205,9 +206,12 @@ __device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int t = page_token<KV, BS>(nt, q4, e);  // token within page
-        float x = s[nt][2 * rs + e] * scale_log2 + slope[rs] * (tok_rel0 + (float)t);
+        float x = s[nt][2 * rs + e] * scale_log2;
+        if constexpr (!PLAIN) x += slope[rs] * (tok_rel0 + (float)t);
         if (TAIL && t >= valid) x = kNegInf;
-        if (!row_on[rs]) x = kNegInf;
+        if constexpr (!PLAIN) {
+          if (!row_on[rs]) x = kNegInf;
+        }
         s[nt][2 * rs + e] = x;
         mx = fmaxf(mx, x);
       }

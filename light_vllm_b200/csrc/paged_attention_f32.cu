@@ -95,7 +95,7 @@ paged_attention_f32_kernel(const __grid_constant__ AttnParams p) {
   const uint64_t policy = l2_policy_evict_first();
 
   auto issue = [&](int i) {
-    if (lane == 0) {
+    if (elect_one()) {
       const int64_t blk = bt[page_begin + warp + i * nwarps];
       const int s = i % NS;
       const uint32_t bar = bars_u32 + 8 * s;

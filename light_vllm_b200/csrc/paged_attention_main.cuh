@@ -3,6 +3,13 @@
 
 #include "paged_attention.cuh"
 
+#ifndef B200_ATTN_MAXT
+#define B200_ATTN_MAXT 256
+#endif
+#ifndef B200_ATTN_MINB
+#define B200_ATTN_MINB 1
+#endif
+
 namespace b200 {
 
 // Load this lane's A-operand fragments of Q for the q-head group (rows = heads, padded to GROWS).
@@ -46,8 +53,8 @@ __device__ __forceinline__ void load_q(uint32_t (&qa)[(D + 15) / 16][GROWS / 4],
 
 // Grid: (splits, KH * gchunks, num_seqs).  v1: `splits` CTAs form one cluster (DSMEM merge).
 // v2: splits = max_num_partitions, each CTA owns one 512-token partition (scratch merge).
-template <typename T, int D, int BS, int KV, int GROWS>
-__global__ void __launch_bounds__(256, 1) paged_attention_kernel(const __grid_constant__ AttnParams p) {
+template <typename T, int D, int BS, int KV, int GROWS, bool PLAIN>
+__global__ void __launch_bounds__(B200_ATTN_MAXT, B200_ATTN_MINB) paged_attention_kernel(const __grid_constant__ AttnParams p) {
   constexpr int ES = KvTraits<KV>::ES;
   constexpr int PAGE_BYTES = D * BS * ES;        // one K (or V) page of one KV head
   constexpr int STAGE_BYTES = 2 * PAGE_BYTES;    // K page + V page
@@ -117,13 +124,12 @@ __global__ void __launch_bounds__(256, 1) paged_attention_kernel(const __grid_co
   };
   int tblA = load_tbl(0), tblB = load_tbl(32);
 
-  auto issue = [&](int i) {  // all lanes call; lane 0 issues
+  auto issue = [&](int i, int s) {  // all lanes call; lane 0 issues page i into ring stage s
     const int src_lane = i & 31;
     const int a = __shfl_sync(0xffffffffu, tblA, src_lane);
     const int b = __shfl_sync(0xffffffffu, tblB, src_lane);
     const int64_t blk = (i < win0 + 32) ? a : b;
-    if (lane == 0) {
-      const int s = i % NS;
+    if (elect_one()) {
       const uint32_t bar = bars_u32 + 8 * s;
       const uint32_t dst = ring_u32 + (uint32_t)s * STAGE_BYTES;
       mbar_arrive_expect_tx(bar, STAGE_BYTES);
@@ -133,7 +139,7 @@ __global__ void __launch_bounds__(256, 1) paged_attention_kernel(const __grid_co
   };
 
   const int pre = min(NS, n_my);
-  for (int i = 0; i < pre; ++i) issue(i);
+  for (int i = 0; i < pre; ++i) issue(i, i);
 
   // ---- Q fragments, running state ----
   uint32_t qa[(D + 15) / 16][GROWS / 4];
@@ -185,7 +191,7 @@ __global__ void __launch_bounds__(256, 1) paged_attention_kernel(const __grid_co
     bool row_on[RS];
 #pragma unroll
     for (int rs = 0; rs < RS; ++rs) row_on[rs] = true;
-    if (p.bs_enabled) {
+    if (!PLAIN && p.bs_enabled) {
       const int k_bs_block_id = tok0 / p.bs_block_size;
 #pragma unroll
       for (int rs = 0; rs < RS; ++rs) {
@@ -197,15 +203,15 @@ __global__ void __launch_bounds__(256, 1) paged_attention_kernel(const __grid_co
     mbar_wait(bars_u32 + 8 * stage, parity);
     const float tok_rel0 = (float)(tok0 - seq_len + 1);
     if (tok0 + BS > seq_len) {
-      process_page<T, D, BS, KV, GROWS, true>(ksm, ksm + PAGE_BYTES, qa, o, m, l, lane,
+      process_page<T, D, BS, KV, GROWS, true, PLAIN>(ksm, ksm + PAGE_BYTES, qa, o, m, l, lane,
                                               seq_len - tok0, p.scale_log2, slope, tok_rel0,
                                               row_on);
     } else {
-      process_page<T, D, BS, KV, GROWS, false>(ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS,
+      process_page<T, D, BS, KV, GROWS, false, PLAIN>(ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS,
                                                p.scale_log2, slope, tok_rel0, row_on);
     }
     __syncwarp();  // every lane is done reading this stage before it is refilled
-    if (i + NS < n_my) issue(i + NS);
+    if (i + NS < n_my) issue(i + NS, stage);  // page i + NS lands in the stage just consumed
     if (++stage == NS) {
       stage = 0;
       parity ^= 1u;
