@@ -71,6 +71,16 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(config_name):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one attention launch, from the committed
+    `ncu --set full` capture of this config (profiles/ncu_traffic.json); None if never captured."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return float(json.load(f)[config_name]["traffic"])
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """SM clock and throttle reasons sampled DURING the timed region (NVML every ~2 ms in a thread;
     falls back to `nvidia-smi -lms` when the NVML binding is unavailable)."""
@@ -559,7 +569,8 @@ def main():
                     "api": "PagedB200AttentionImpl.forward per layer pool, pinned host q/k/v + "
                            "metadata in, output read back"},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
-                         "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None,
+                         "unit": "GB/s", "frac": round(achieved / peak, 4),
+                         "traffic": None if (args.ctx or args.batch) else ncu_traffic(args.config),
                          "kernel": f"paged_attention_v{c['version']} (attention launch alone, "
                                    f"{algorithmic_bytes_attention(c)} algorithmic bytes)",
                          "us_per_launch": round(r["ms_attn"] * 1e3, 2), "peak_source": peak_src,
