@@ -1,0 +1,68 @@
+"""BASELINE.json configs[0] (Qwen2-0.5B-shaped greedy decode over the paged cache) at unit-test
+size: the harness against a paging-free dense recomputation (CPU), and the B200 plugin against
+the reference's CPU kernels (GPU)."""
+import pytest
+import torch
+
+from qwen2_harness import (B200Engine, CpuEngine, Qwen2Shape, dense_reference, greedy_decode,
+                           init_weights, make_block_tables, make_prompts)
+
+BS = 16
+
+
+def _setup(batch=4, prompt_len=37, new=12):
+    shape = Qwen2Shape.tiny()
+    w = init_weights(shape, 0)
+    prompts = make_prompts(batch, prompt_len, shape.vocab, seed=1)
+    prompts[1] = prompts[1][:9]            # ragged prompts
+    prompts[2] = prompts[2][:BS]           # exactly one block
+    bt, nb = make_block_tables(batch, prompt_len + new, BS, seed=2)
+    return shape, w, prompts, bt, nb, new
+
+
+def _cpu_mods():
+    from oracle import oracle, ref
+    mods = [("oracle", oracle)]
+    if ref.have_ref_cpu():
+        mods.append(("reference_cpu", ref.ref_cpu()))
+    return mods
+
+
+def test_paged_cpu_engines_match_dense_recompute():
+    shape, w, prompts, bt, nb, new = _setup()
+    want = dense_reference(shape, w, prompts, new)
+    for name, mod in _cpu_mods():
+        got = greedy_decode(shape, w, CpuEngine(mod, shape, nb, BS, torch.float32), prompts, new,
+                            BS, bt)["tokens"]
+        assert torch.equal(got, want), name
+
+
+@pytest.mark.gpu
+def test_b200_fp32_matches_cpu_reference_tokens_and_attention():
+    shape, w, prompts, bt, nb, new = _setup()
+    name, mod = _cpu_mods()[-1]
+    cpu = greedy_decode(shape, w, CpuEngine(mod, shape, nb, BS, torch.float32), prompts, new, BS,
+                        bt, record=True)
+    wd = {k: v.cuda() for k, v in w.items()}
+    gpu = greedy_decode(shape, wd, B200Engine(shape, nb, BS, torch.float32, "cuda"), prompts, new,
+                        BS, bt, device="cuda", record=True)
+    assert torch.equal(gpu["tokens"], cpu["tokens"]), f"greedy tokens differ from {name}"
+    for a, b in zip(gpu["attn"], cpu["attn"]):
+        assert (a - b).abs().max().item() <= 1e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol,agree", [(torch.float16, 1e-2, 0.9), (torch.bfloat16, 5e-2, 0.75)])
+def test_b200_16bit_teacher_forced(dtype, tol, agree):
+    """16-bit weights/activations drift from the fp32 CPU run layer by layer, so the continuation
+    is teacher-forced with the CPU tokens and compared per step."""
+    shape, w, prompts, bt, nb, new = _setup()
+    _, mod = _cpu_mods()[-1]
+    cpu = greedy_decode(shape, w, CpuEngine(mod, shape, nb, BS, torch.float32), prompts, new, BS,
+                        bt, record=True)
+    wd = {k: v.to("cuda", dtype) for k, v in w.items()}
+    gpu = greedy_decode(shape, wd, B200Engine(shape, nb, BS, dtype, "cuda"), prompts, new, BS, bt,
+                        device="cuda", forced=cpu["tokens"], record=True)
+    for a, b in zip(gpu["attn"], cpu["attn"]):
+        assert (a - b).abs().max().item() <= tol
+    assert (gpu["tokens"] == cpu["tokens"]).float().mean().item() >= agree
