@@ -167,6 +167,51 @@ int b200_convert_fp8(void* dst, const void* src, int64_t numel, float scale, int
                      int kv_dtype, int to_fp8, int device, b200_stream_t stream);
 
 /*
+ * advance_step — replaces torch.ops._C.advance_step
+ *   (csrc/torch_bindings.cpp:75-77, csrc/prepare_inputs/advance_step.cu:15-130).
+ *   For every query i < num_queries: input_tokens[i] = sampled_token_ids[i]; seq_lens[i] += 1;
+ *   input_positions[i] = seq_lens[i] - 1; slot_mapping[i] = block_tables[i][pos / block_size] *
+ *   block_size + pos % block_size.  All device pointers; block_tables row stride in elements.
+ *   Lets the next decode step's inputs be produced on the GPU (no host round trip, graph-capturable).
+ */
+int b200_advance_step(int num_seqs, int num_queries, int block_size, int64_t* input_tokens,
+                      const int64_t* sampled_token_ids, int64_t* input_positions,
+                      int32_t* seq_lens, int64_t* slot_mapping, const int32_t* block_tables,
+                      int64_t block_tables_stride, int device, b200_stream_t stream);
+
+/*
+ * rotary_embedding — replaces torch.ops._C.rotary_embedding and, with cos_sin_cache_offsets != NULL,
+ *   torch.ops._C.batched_rotary_embedding (csrc/torch_bindings.cpp:93-108,
+ *   csrc/pos_encoding_kernels.cu:9-200).  In-place GPT-NeoX (is_neox) or GPT-J rotation of the first
+ *   rot_dim elements of every head of query [num_tokens, num_heads, head_size] and key
+ *   [num_tokens, num_kv_heads, head_size] (token strides in elements); cos_sin_cache
+ *   [max_position, rot_dim] of the same dtype; positions int64 [num_tokens].
+ *   Rounding as the reference: products and the sum/difference are each rounded to the tensor dtype.
+ */
+int b200_rotary_embedding(const int64_t* positions, void* query, void* key,
+                          const void* cos_sin_cache, const int64_t* cos_sin_cache_offsets,
+                          int num_tokens, int num_heads, int num_kv_heads, int head_size,
+                          int rot_dim, int64_t query_stride, int64_t key_stride, int is_neox,
+                          int dtype, int device, b200_stream_t stream);
+
+/*
+ * rotary_reshape_and_cache — rotary_embedding followed by reshape_and_cache (both above) as ONE
+ *   launch: the two reference ops light-vllm issues back to back for every layer
+ *   (decode_only/modelzoo/qwen2.py:150-154 -> layers/rotary_embedding.py, then
+ *   cache_kernels.cu:152-204).  query/key are rotated in place; the rotated key and `value` are
+ *   scattered into the paged caches at slot_mapping (slot < 0: rotated but not cached), with the
+ *   fp8 quantisation of reshape_and_cache.  Bit-identical to the two-op sequence.
+ */
+int b200_rotary_reshape_and_cache(const int64_t* positions, void* query, void* key,
+                                  const void* value, const void* cos_sin_cache,
+                                  const int64_t* cos_sin_cache_offsets, void* key_cache,
+                                  void* value_cache, const int64_t* slot_mapping, int num_tokens,
+                                  int num_heads, int num_kv_heads, int head_size, int rot_dim,
+                                  int block_size, int x, int64_t query_stride, int64_t key_stride,
+                                  int64_t value_stride, int is_neox, float k_scale, float v_scale,
+                                  int dtype, int kv_dtype, int device, b200_stream_t stream);
+
+/*
  * get_device_attribute / get_max_shared_memory_per_block_device_attribute — replace
  *   torch.ops._C_cuda_utils.* (csrc/torch_bindings.cpp:271-279, csrc/cuda_utils_kernels.cu:8-29).
  *   Return the attribute value, or -1 on error.

@@ -92,6 +92,43 @@ def convert_fp8(output: torch.Tensor, input: torch.Tensor, scale: float = 1.0,
     _cache.convert_fp8(output, input, scale, kv_dtype)
 
 
+def rotary_embedding_reshape_and_cache(positions: torch.Tensor, query: torch.Tensor,
+                                       key: torch.Tensor, value: torch.Tensor, head_size: int,
+                                       cos_sin_cache: torch.Tensor, is_neox: bool,
+                                       key_cache: torch.Tensor, value_cache: torch.Tensor,
+                                       slot_mapping: torch.Tensor, kv_cache_dtype: str,
+                                       k_scale: float, v_scale: float) -> None:
+    """B200 extension: ``rotary_embedding`` then ``reshape_and_cache`` in ONE launch -- q and k are
+    rotated in place, the rotated k and v land in the paged cache (fp8 quantisation included).
+    Bit-identical to calling the two reference ops back to back."""
+    _cache.rotary_embedding_reshape_and_cache(positions, query, key, value, head_size,
+                                              cos_sin_cache, is_neox, key_cache, value_cache,
+                                              slot_mapping, kv_cache_dtype, k_scale, v_scale)
+
+
+# ------------------------------------------------------------------- per-step ops ----
+# Same names / arguments as light_vllm/backends/_custom_ops.py:134-153,167-176.
+def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                     head_size: int, cos_sin_cache: torch.Tensor, is_neox: bool) -> None:
+    _attn.rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox)
+
+
+def batched_rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                             head_size: int, cos_sin_cache: torch.Tensor, is_neox: bool,
+                             rot_dim: int, cos_sin_cache_offsets: torch.Tensor) -> None:
+    _attn.batched_rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox,
+                                   rot_dim, cos_sin_cache_offsets)
+
+
+def advance_step(num_seqs: int, num_queries: int, block_size: int, input_tokens: torch.Tensor,
+                 sampled_token_ids: torch.Tensor, input_positions: torch.Tensor,
+                 seq_lens: torch.Tensor, slot_mapping: torch.Tensor,
+                 block_tables: torch.Tensor) -> None:
+    """Advance a step on GPU for existing inputs for a multi-step runner"""
+    return _attn.advance_step(num_seqs, num_queries, block_size, input_tokens, sampled_token_ids,
+                              input_positions, seq_lens, slot_mapping, block_tables)
+
+
 # ---------------------------------------------------------------- device attributes ----
 def get_device_attribute(attribute: int, device: int) -> int:
     return _cuda_utils.get_device_attribute(attribute, device)

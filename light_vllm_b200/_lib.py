@@ -33,6 +33,9 @@ ABI_SYMBOLS = (
     "b200_copy_blocks",
     "b200_swap_blocks",
     "b200_convert_fp8",
+    "b200_advance_step",
+    "b200_rotary_embedding",
+    "b200_rotary_reshape_and_cache",
     "b200_get_device_attribute",
     "b200_get_max_shared_memory_per_block_device_attribute",
     "b200_paged_attention_plan",

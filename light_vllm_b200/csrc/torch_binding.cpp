@@ -322,6 +322,133 @@ void convert_fp8(torch::Tensor& dst_cache, torch::Tensor& src_cache, const doubl
                          cur_stream()));
 }
 
+// torch.ops._C.advance_step (csrc/ops.h:57-60, csrc/prepare_inputs/advance_step.cu:75-130)
+void verify_tensor(const char* name, const torch::Tensor& t, int64_t size_0, int64_t size_1,
+                   c10::ScalarType type) {
+  const bool ok = (size_0 == -1 || t.size(0) == size_0) &&
+                  (size_1 == -1 || (t.dim() > 1 && t.size(1) == size_1)) && t.is_contiguous() &&
+                  t.scalar_type() == type && t.is_cuda();
+  TORCH_CHECK(ok, "tensor: name = ", name, ", shape = ", t.sizes(), " is_cont = ",
+              t.is_contiguous(), ", type = ", t.dtype(), " is not as expected: shape = [", size_0,
+              ", ", size_1, "], type = ", type);
+}
+
+void advance_step(int64_t num_seqs, int64_t num_queries, int64_t block_size,
+                  torch::Tensor& input_tokens, torch::Tensor& sampled_token_ids,
+                  torch::Tensor& input_positions, torch::Tensor& seq_lens,
+                  torch::Tensor& slot_mapping, torch::Tensor& block_tables) {
+  verify_tensor("input_tokens", input_tokens, num_seqs, -1, at::kLong);
+  verify_tensor("sampled_token_ids", sampled_token_ids, num_queries, 1, at::kLong);
+  verify_tensor("input_positions", input_positions, num_seqs, -1, at::kLong);
+  verify_tensor("seq_lens", seq_lens, num_seqs, -1, at::kInt);
+  verify_tensor("slot_mapping", slot_mapping, num_seqs, -1, at::kLong);
+  verify_tensor("block_tables", block_tables, num_seqs, -1, at::kInt);
+  const at::cuda::OptionalCUDAGuard guard(device_of(sampled_token_ids));
+  check(b200_advance_step((int)num_seqs, (int)num_queries, (int)block_size,
+                          input_tokens.data_ptr<int64_t>(), sampled_token_ids.data_ptr<int64_t>(),
+                          input_positions.data_ptr<int64_t>(), seq_lens.data_ptr<int32_t>(),
+                          slot_mapping.data_ptr<int64_t>(), block_tables.data_ptr<int32_t>(),
+                          block_tables.stride(0), sampled_token_ids.get_device(), cur_stream()));
+}
+
+struct RopeArgs {
+  int num_tokens, num_heads, num_kv_heads, rot_dim, dtype;
+  int64_t query_stride, key_stride;
+};
+
+RopeArgs unpack_rope(const torch::Tensor& positions, const torch::Tensor& query,
+                     const torch::Tensor& key, int64_t head_size,
+                     const torch::Tensor& cos_sin_cache, int64_t num_tokens) {
+  TORCH_CHECK(positions.is_cuda() && query.is_cuda() && key.is_cuda() && cos_sin_cache.is_cuda(),
+              "rotary_embedding: all tensors must be CUDA tensors");
+  TORCH_CHECK(positions.scalar_type() == at::kLong && positions.is_contiguous(),
+              "positions must be a contiguous int64 tensor");
+  TORCH_CHECK(query.scalar_type() == key.scalar_type() &&
+                  query.scalar_type() == cos_sin_cache.scalar_type(),
+              "query, key and cos_sin_cache must share one dtype");
+  TORCH_CHECK(cos_sin_cache.dim() == 2 && cos_sin_cache.is_contiguous(),
+              "cos_sin_cache must be a contiguous [max_position, rot_dim] tensor");
+  TORCH_CHECK(query.stride(-1) == 1 && key.stride(-1) == 1 && head_size > 0 &&
+                  query.size(-1) % head_size == 0 && key.size(-1) % head_size == 0,
+              "query/key last dim must be dense and a multiple of head_size");
+  RopeArgs a{};
+  a.num_tokens = (int)num_tokens;
+  a.num_heads = (int)(query.size(-1) / head_size);
+  a.num_kv_heads = (int)(key.size(-1) / head_size);
+  a.rot_dim = (int)cos_sin_cache.size(1);
+  a.query_stride = query.stride(-2);
+  a.key_stride = key.stride(-2);
+  a.dtype = dt_code(query.scalar_type(), "query");
+  return a;
+}
+
+// torch.ops._C.rotary_embedding (csrc/ops.h:35-37, pos_encoding_kernels.cu:119-160)
+void rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key,
+                      int64_t head_size, torch::Tensor& cos_sin_cache, bool is_neox) {
+  const RopeArgs a = unpack_rope(positions, query, key, head_size, cos_sin_cache,
+                                 query.numel() / query.size(-1));
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  check(b200_rotary_embedding(positions.data_ptr<int64_t>(), query.data_ptr(), key.data_ptr(),
+                              cos_sin_cache.data_ptr(), nullptr, a.num_tokens, a.num_heads,
+                              a.num_kv_heads, (int)head_size, a.rot_dim, a.query_stride,
+                              a.key_stride, is_neox ? 1 : 0, a.dtype, query.get_device(),
+                              cur_stream()));
+}
+
+// torch.ops._C.batched_rotary_embedding (csrc/ops.h:39-43, pos_encoding_kernels.cu:166-200)
+void batched_rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key,
+                              int64_t head_size, torch::Tensor& cos_sin_cache, bool is_neox,
+                              int64_t rot_dim, torch::Tensor& cos_sin_cache_offsets) {
+  TORCH_CHECK(cos_sin_cache_offsets.is_cuda() && cos_sin_cache_offsets.scalar_type() == at::kLong &&
+                  cos_sin_cache_offsets.is_contiguous(),
+              "cos_sin_cache_offsets must be a contiguous int64 CUDA tensor");
+  RopeArgs a = unpack_rope(positions, query, key, head_size, cos_sin_cache,
+                           cos_sin_cache_offsets.size(0));
+  a.rot_dim = (int)rot_dim;  // the batched op takes rot_dim explicitly (:176,:183)
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  check(b200_rotary_embedding(positions.data_ptr<int64_t>(), query.data_ptr(), key.data_ptr(),
+                              cos_sin_cache.data_ptr(), cos_sin_cache_offsets.data_ptr<int64_t>(),
+                              a.num_tokens, a.num_heads, a.num_kv_heads, (int)head_size, a.rot_dim,
+                              a.query_stride, a.key_stride, is_neox ? 1 : 0, a.dtype,
+                              query.get_device(), cur_stream()));
+}
+
+// torch.ops._C_cache_ops.rotary_embedding_reshape_and_cache: B200 extension = rotary_embedding +
+// reshape_and_cache in one launch (arguments = the union of the two reference ops).
+void rotary_embedding_reshape_and_cache(torch::Tensor& positions, torch::Tensor& query,
+                                        torch::Tensor& key, torch::Tensor& value, int64_t head_size,
+                                        torch::Tensor& cos_sin_cache, bool is_neox,
+                                        torch::Tensor& key_cache, torch::Tensor& value_cache,
+                                        torch::Tensor& slot_mapping,
+                                        const std::string& kv_cache_dtype, const double k_scale,
+                                        const double v_scale) {
+  const RopeArgs a = unpack_rope(positions, query, key, head_size, cos_sin_cache,
+                                 query.numel() / query.size(-1));
+  TORCH_CHECK(value.is_cuda() && key_cache.is_cuda() && value_cache.is_cuda() &&
+                  slot_mapping.is_cuda(), "rotary_embedding_reshape_and_cache: CUDA tensors only");
+  TORCH_CHECK(value.scalar_type() == key.scalar_type() && value.stride(-1) == 1 &&
+                  value.size(-1) == key.size(-1), "value must match key in dtype and width");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::kLong && slot_mapping.is_contiguous() &&
+                  slot_mapping.numel() >= a.num_tokens,
+              "slot_mapping must be a contiguous int64 tensor of num_tokens entries");
+  TORCH_CHECK(key_cache.dim() == 5 && value_cache.dim() == 4 && key_cache.is_contiguous() &&
+                  value_cache.is_contiguous(),
+              "caches must be dense [nb, kh, d/x, bs, x] and [nb, kh, d, bs]");
+  const int kv = kv_code(kv_cache_dtype);
+  check_cache_dtype(key, key_cache, kv);
+  check_cache_dtype(key, value_cache, kv);
+  TORCH_CHECK(key_cache.size(1) == a.num_kv_heads && value_cache.size(2) == head_size,
+              "cache shape does not match key heads / head_size");
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  check(b200_rotary_reshape_and_cache(
+      positions.data_ptr<int64_t>(), query.data_ptr(), key.data_ptr(), value.data_ptr(),
+      cos_sin_cache.data_ptr(), nullptr, key_cache.data_ptr(), value_cache.data_ptr(),
+      slot_mapping.data_ptr<int64_t>(), a.num_tokens, a.num_heads, a.num_kv_heads, (int)head_size,
+      a.rot_dim, (int)key_cache.size(3), (int)key_cache.size(4), a.query_stride, a.key_stride,
+      value.stride(-2), is_neox ? 1 : 0, (float)k_scale, (float)v_scale, a.dtype, kv,
+      query.get_device(), cur_stream()));
+}
+
 int64_t get_device_attribute(int64_t attribute, int64_t device_id) {
   const int64_t v = b200_get_device_attribute(attribute, device_id);
   TORCH_CHECK(v >= 0, b200_last_error());
@@ -359,6 +486,21 @@ TORCH_LIBRARY_FRAGMENT(_C, ops) {
       "    int blocksparse_vert_stride, int blocksparse_block_size,"
       "    int blocksparse_head_sliding_step) -> ()");
   ops.impl("paged_attention_v2", torch::kCUDA, &paged_attention_v2);
+  // adjacent per-step ops (csrc/torch_bindings.cpp:75-77, 93-108)
+  ops.def("advance_step", &advance_step);
+  ops.impl("advance_step", torch::kCUDA, &advance_step);
+  ops.def(
+      "rotary_embedding(Tensor positions, Tensor! query,"
+      "                 Tensor! key, int head_size,"
+      "                 Tensor cos_sin_cache, bool is_neox) -> ()");
+  ops.impl("rotary_embedding", torch::kCUDA, &rotary_embedding);
+  ops.def(
+      "batched_rotary_embedding(Tensor positions, Tensor! query,"
+      "                         Tensor! key, int head_size,"
+      "                         Tensor cos_sin_cache, bool is_neox,"
+      "                         int rot_dim,"
+      "                         Tensor cos_sin_cache_offsets) -> ()");
+  ops.impl("batched_rotary_embedding", torch::kCUDA, &batched_rotary_embedding);
 }
 
 TORCH_LIBRARY_FRAGMENT(_C_cache_ops, cache_ops) {
@@ -385,6 +527,15 @@ TORCH_LIBRARY_FRAGMENT(_C_cache_ops, cache_ops) {
   cache_ops.def(
       "convert_fp8(Tensor! dst_cache, Tensor src_cache, float scale, str kv_cache_dtype) -> ()");
   cache_ops.impl("convert_fp8", torch::kCUDA, &convert_fp8);
+  // B200 extension: rotary_embedding + reshape_and_cache in one launch
+  cache_ops.def(
+      "rotary_embedding_reshape_and_cache(Tensor positions, Tensor! query, Tensor! key,"
+      "                                   Tensor value, int head_size, Tensor cos_sin_cache,"
+      "                                   bool is_neox, Tensor! key_cache, Tensor! value_cache,"
+      "                                   Tensor slot_mapping, str kv_cache_dtype,"
+      "                                   float k_scale, float v_scale) -> ()");
+  cache_ops.impl("rotary_embedding_reshape_and_cache", torch::kCUDA,
+                 &rotary_embedding_reshape_and_cache);
 }
 
 TORCH_LIBRARY_FRAGMENT(_C_cuda_utils, cuda_utils) {

@@ -148,3 +148,34 @@ def convert_fp8(output, input, scale=1.0, kv_dtype="fp8"):
     rc = lib().oracle_convert_fp8(_p(output), _p(input), _i64(input.numel()), _f(scale), _DT[wide],
                                   _KV[kv_dtype], 1 if to_fp8 else 0)
     assert rc == 0
+
+
+# ---------------------------------------------------------------- per-step ops (8f) ----
+def advance_step(num_seqs, num_queries, block_size, input_tokens, sampled_token_ids,
+                 input_positions, seq_lens, slot_mapping, block_tables):
+    assert input_tokens.dtype == torch.int64 and seq_lens.dtype == torch.int32
+    assert block_tables.dtype == torch.int32 and block_tables.is_contiguous()
+    rc = lib().oracle_advance_step(
+        int(num_seqs), int(num_queries), int(block_size), _p(input_tokens), _p(sampled_token_ids),
+        _p(input_positions), _p(seq_lens), _p(slot_mapping), _p(block_tables),
+        _i64(block_tables.stride(0)))
+    assert rc == 0
+
+
+def rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox, rot_dim=None,
+                     cos_sin_cache_offsets=None):
+    """rotary_embedding / batched_rotary_embedding (with offsets) of the reference, in place."""
+    num_tokens = query.numel() // query.shape[-1]
+    assert positions.dtype == torch.int64 and query.stride(-1) == 1 and key.stride(-1) == 1
+    rc = lib().oracle_rotary_embedding(
+        _p(positions), _p(query), _p(key), _p(cos_sin_cache), _p(cos_sin_cache_offsets),
+        int(num_tokens), query.shape[-1] // head_size, key.shape[-1] // head_size, int(head_size),
+        int(rot_dim if rot_dim is not None else cos_sin_cache.shape[1]), _i64(query.stride(-2)),
+        _i64(key.stride(-2)), 1 if is_neox else 0, _DT[query.dtype])
+    assert rc == 0
+
+
+def batched_rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox, rot_dim,
+                             cos_sin_cache_offsets):
+    rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox, rot_dim,
+                     cos_sin_cache_offsets)

@@ -386,3 +386,70 @@ int oracle_paged_attention_v2(void* out, float* exp_sums, float* max_logits, voi
     }
   return 0;
 }
+
+/* ------------------------------------------------------------------ per-step ops ------ */
+/* advance_step_kernel (csrc/prepare_inputs/advance_step.cu:15-58): per query, next token in,
+ * seq_len + 1, position = new seq_len - 1, slot from the block table -- 32-bit int arithmetic. */
+int oracle_advance_step(int num_seqs, int num_queries, int block_size, int64_t* input_tokens,
+                        const int64_t* sampled_token_ids, int64_t* input_positions,
+                        int32_t* seq_lens, int64_t* slot_mapping, const int32_t* block_tables,
+                        int64_t block_tables_stride) {
+  (void)num_seqs;
+  for (int q = 0; q < num_queries; ++q) {
+    input_tokens[q] = sampled_token_ids[q];                       /* :35 */
+    const int next_seq_len = seq_lens[q] + 1;                     /* :37-39 */
+    const int next_pos = next_seq_len - 1;
+    seq_lens[q] = next_seq_len;                                   /* :42 */
+    input_positions[q] = next_pos;                                /* :44 */
+    const int32_t* bt = block_tables + block_tables_stride * q;   /* :46-47 */
+    const int slot = bt[next_pos / block_size] * block_size + next_pos % block_size; /* :49-53 */
+    slot_mapping[q] = slot;                                       /* :55 */
+  }
+  return 0;
+}
+
+/* apply_token_rotary_embedding (csrc/pos_encoding_kernels.cu:10-36).  scalar_t arithmetic of the
+ * reference: for c10::Half / c10::BFloat16 every operator computes in float and rounds back to T
+ * (three roundings per output); for float nvcc contracts `x*cos - y*sin` to fma(x, cos, -(y*sin))
+ * and `y*cos + x*sin` to fma(x, sin, y*cos) (SASS of all four float instantiations of the file
+ * compiled for sm_100a). */
+static void rotate_pair(void* arr, int64_t xi, int64_t yi, float c, float s, int dt) {
+  const float x = load_elem(arr, xi, dt), y = load_elem(arr, yi, dt);
+  float ox, oy;
+  if (dt == DT_F32) {
+    ox = fmaf(x, c, -(y * s));
+    oy = fmaf(x, s, y * c);
+  } else {
+    ox = round_to(x * c, dt) - round_to(y * s, dt);
+    oy = round_to(y * c, dt) + round_to(x * s, dt);
+  }
+  store_elem(arr, xi, dt, ox);
+  store_elem(arr, yi, dt, oy);
+}
+
+/* rotary_embedding_kernel / batched_rotary_embedding_kernel (pos_encoding_kernels.cu:73-116):
+ * in place on query [T, H, head_size] and key [T, KH, head_size] (token strides in elements);
+ * cos_sin_cache [max_position, rot_dim] = cos | sin halves; offsets may be NULL. */
+int oracle_rotary_embedding(const int64_t* positions, void* query, void* key,
+                            const void* cos_sin_cache, const int64_t* offsets, int num_tokens,
+                            int num_heads, int num_kv_heads, int head_size, int rot_dim,
+                            int64_t query_stride, int64_t key_stride, int is_neox, int dt) {
+  const int embed = rot_dim / 2;
+  for (int64_t t = 0; t < num_tokens; ++t) {
+    const int64_t pos = positions[t] + (offsets ? offsets[t] : 0);
+    const int64_t cbase = pos * rot_dim;
+    for (int pass = 0; pass < 2; ++pass) {
+      void* arr = pass == 0 ? query : key;
+      const int heads = pass == 0 ? num_heads : num_kv_heads;
+      const int64_t stride = pass == 0 ? query_stride : key_stride;
+      for (int h = 0; h < heads; ++h)
+        for (int r = 0; r < embed; ++r) {
+          const int64_t base = t * stride + (int64_t)h * head_size;
+          const int64_t xi = is_neox ? r : 2 * r, yi = is_neox ? embed + r : 2 * r + 1; /* :16-28 */
+          rotate_pair(arr, base + xi, base + yi, load_elem(cos_sin_cache, cbase + r, dt),
+                      load_elem(cos_sin_cache, cbase + embed + r, dt), dt);
+        }
+    }
+  }
+  return 0;
+}
