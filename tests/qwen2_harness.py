@@ -288,3 +288,115 @@ def dense_reference(shape, weights, prompts, new_tokens):
             s.append(t)
         out.append(step)
     return torch.tensor(out).t()
+
+
+class GraphDecoder:
+    """One whole decode step as ONE CUDA graph: no host work per token.
+
+    Graph body, all on static device buffers: embedding -> per layer [RMSNorm, QKV, fused
+    rotary_embedding_reshape_and_cache, paged_attention (plan fixed by ``max_len``), O, MLP] ->
+    logits -> argmax -> ``advance_step`` (next token, position, seq_len and slot computed on the
+    GPU from the block table).  Each replay consumes the previous replay's outputs."""
+
+    def __init__(self, shape: Qwen2Shape, weights, engine: "B200Engine", block_size: int,
+                 block_tables: torch.Tensor, max_len: int, dtype, device="cuda"):
+        from light_vllm_b200 import _custom_ops as ops
+        from light_vllm_b200.attention import PagedAttention
+        self.shape, self.w, self.eng, self.bs, self.max_len = shape, weights, engine, block_size, max_len
+        self.ops, self.PA = ops, PagedAttention
+        B = block_tables.shape[0]
+        self.B = B
+        self.tok = torch.zeros(B, dtype=torch.long, device=device)
+        self.pos = torch.zeros(B, dtype=torch.long, device=device)
+        self.seq_lens = torch.zeros(B, dtype=torch.int32, device=device)
+        self.slots = torch.zeros(B, dtype=torch.long, device=device)
+        self.sampled = torch.zeros(B, 1, dtype=torch.long, device=device)
+        self.bt = block_tables.to(device).contiguous()
+        D = shape.head_dim
+        inv = 1.0 / (shape.rope_theta ** (torch.arange(0, D, 2, dtype=torch.float) / D))
+        fr = torch.outer(torch.arange(max_len + 1, dtype=torch.float), inv)
+        self.cos_sin = torch.cat((fr.cos(), fr.sin()), dim=-1).to(device=device, dtype=dtype)
+        self.caches = [PagedAttention.split_kv_cache(p, shape.kv_heads, D) for p in engine.pools]
+        self.graph = None
+
+    def _step(self):
+        sh, w, ops = self.shape, self.w, self.ops
+        H, KH, D = sh.heads, sh.kv_heads, sh.head_dim
+        x = w["emb"][self.tok]
+        for l in range(sh.layers):
+            h = rmsnorm(x, w[f"l{l}.ln1"], sh.eps)
+            qkv = F.linear(h, w[f"l{l}.qkv"], w[f"l{l}.qkv_b"])
+            q, k, v = qkv.split([H * D, KH * D, KH * D], dim=-1)
+            kc, vc = self.caches[l]
+            ops.rotary_embedding_reshape_and_cache(self.pos, q, k, v, D, self.cos_sin, True, kc, vc,
+                                                   self.slots, "auto", 1.0, 1.0)
+            o = self.PA.forward_decode(q.view(-1, H, D), kc, vc, self.bt, self.seq_lens,
+                                       self.max_len, "auto", KH, D ** -0.5, None, 1.0, 1.0)
+            x = x + F.linear(o.reshape(-1, H * D), w[f"l{l}.o"])
+            h = rmsnorm(x, w[f"l{l}.ln2"], sh.eps)
+            gate, up = F.linear(h, w[f"l{l}.gate_up"]).chunk(2, dim=-1)
+            x = x + F.linear(F.silu(gate) * up, w[f"l{l}.down"])
+        logits = F.linear(rmsnorm(x, w["norm"], sh.eps), w["head"])
+        self.sampled.copy_(logits.float().argmax(-1, keepdim=True))
+        # next step's inputs, on the GPU: tok <- sampled, seq_len += 1, pos, slot from block table
+        ops.advance_step(self.B, self.B, self.bs, self.tok, self.sampled, self.pos, self.seq_lens,
+                         self.slots, self.bt)
+
+    def start(self, first_tokens: torch.Tensor, lens: List[int]):
+        """State after prefill: feed ``first_tokens`` at positions ``lens`` (seq_len becomes len+1)."""
+        dev = self.tok.device
+        self.tok.copy_(first_tokens)
+        self.pos.copy_(torch.tensor(lens, dtype=torch.long))
+        self.seq_lens.copy_(torch.tensor([n + 1 for n in lens], dtype=torch.int32))
+        bt = self.bt.cpu()
+        self.slots.copy_(torch.tensor([int(bt[i, n // self.bs]) * self.bs + n % self.bs
+                                       for i, n in enumerate(lens)], dtype=torch.long))
+        self._saved = [t.clone() for t in (self.tok, self.pos, self.seq_lens, self.slots)]
+        if self.graph is None:
+            s = torch.cuda.Stream(device=dev)
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):       # warm-up outside capture (lazy init, autotune)
+                self._step()
+            torch.cuda.current_stream().wait_stream(s)
+            self._restore()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self._step()
+            self._restore()                  # capture does not execute, but keep state explicit
+
+    def _restore(self):
+        for t, s in zip((self.tok, self.pos, self.seq_lens, self.slots), self._saved):
+            t.copy_(s)
+
+    @torch.inference_mode()
+    def run(self, new_tokens: int) -> torch.Tensor:
+        """``new_tokens`` graph replays; returns the sampled tokens [B, new_tokens] (CPU)."""
+        out = torch.empty(self.B, new_tokens, dtype=torch.long, device=self.tok.device)
+        for step in range(new_tokens):
+            self.graph.replay()
+            out[:, step].copy_(self.sampled[:, 0])
+        torch.cuda.synchronize()
+        return out.cpu()
+
+
+@torch.inference_mode()
+def graph_decode(shape, weights, prompts, new_tokens, block_size, block_tables, num_blocks, dtype,
+                 device="cuda"):
+    """Eager prefill through the plugin, then CUDA-graph decode.  Returns tokens [B, new_tokens]
+    (the first is the prefill's argmax, as in ``greedy_decode``) and the decode wall time."""
+    eng = B200Engine(shape, num_blocks, block_size, dtype, device)
+    pre = greedy_decode(shape, weights, eng, prompts, 1, block_size, block_tables, device=device)
+    # greedy_decode(.., 1) ran the prefill and ONE decode step (its KV is rewritten identically below)
+    first = pre["tokens"][:, 0]
+    lens = [len(p) for p in prompts]
+    dec = GraphDecoder(shape, weights, eng, block_size, block_tables,
+                       max(lens) + new_tokens, dtype, device)
+    dec.start(first.to(device), lens)
+    dec.run(2)                               # warm replays
+    dec._restore()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    rest = dec.run(new_tokens - 1)
+    decode_s = time.perf_counter() - t0
+    return dict(tokens=torch.cat([first[:, None], rest], dim=1), decode_s=decode_s,
+                steps=new_tokens - 1)

@@ -25,8 +25,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from qwen2_harness import (B200Engine, CpuEngine, Qwen2Shape, greedy_decode, init_weights,  # noqa: E402
-                           make_block_tables, make_prompts)
+from qwen2_harness import (B200Engine, CpuEngine, Qwen2Shape, graph_decode, greedy_decode,  # noqa: E402
+                           init_weights, make_block_tables, make_prompts)
 
 
 def first_divergence(a, b):
@@ -84,6 +84,14 @@ def main():
                 (forced["tokens"] == cpu["tokens"]).float().mean().item(), 4),
             "attn_out_max_abs_vs_cpu_per_step": {"max": max(errs), "first": errs[0], "last": errs[-1]},
             "b200_kernel_launches": int(launches)}
+        # the same decode with the whole step in ONE CUDA graph (fused rotary+cache write, paged
+        # attention, advance_step on the GPU): no host work per token
+        gr = graph_decode(shape, wd, prompts, args.new, BS, bt, nb, dtype)
+        res[str(dtype).replace("torch.", "b200_") + "_cuda_graph"] = {
+            "decode_s": round(gr["decode_s"], 4), "steps": gr["steps"],
+            "decode_tokens_per_s": round(args.batch * gr["steps"] / gr["decode_s"], 1),
+            "tokens_equal_eager": bool(torch.equal(gr["tokens"], free["tokens"])),
+            "tokens_equal_cpu": bool(torch.equal(gr["tokens"], cpu["tokens"]))}
         del wd, eng
     print(json.dumps(res))
 
