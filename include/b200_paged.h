@@ -219,6 +219,47 @@ int b200_rotary_reshape_and_cache(const int64_t* positions, void* query, void* k
 int64_t b200_get_device_attribute(int64_t attribute, int64_t device_id);
 int64_t b200_get_max_shared_memory_per_block_device_attribute(int64_t device_id);
 
+/*
+ * Context-sharded decode (one sequence whose KV pages are spread over several
+ * GPUs).  No reference twin: the reference keeps a sequence's pool on one device; the merge is
+ * the reference's own v2 formula (attention_kernels.cu:565-669) applied across ranks.
+ *
+ *   b200_paged_attention_ctx_shard — every rank calls it in the same order with the pages IT owns:
+ *   block_tables / local_seq_lens describe the local slice (0 tokens is fine), the scratch tensors
+ *   are v2's ([B,H,P], [B,H,P], [B,H,P,D]; P >= ceil(max_local_seq_len / 512), >= 1).  The rank's
+ *   partitions are folded into one (max, sum, out) triple per (seq, head), stored straight into
+ *   every peer's exchange buffer over NVLink, and merged after an epoch-flag handshake — one kernel
+ *   after the partition pass, no NCCL, no host synchronisation.  `out` on EVERY rank receives the
+ *   attention over the whole context.  ALiBi and blocksparse are not defined for shards.
+ *     exchange_bufs [world] host array: this process's addresses of every rank's exchange buffer
+ *                   (own buffer from b200_peer_alloc, peers' from b200_peer_open)
+ *     max_pairs     (seq, head) capacity the buffers were sized for (b200_ctx_exchange_bytes)
+ *     epoch         1, 2, 3, ... incremented by the caller on every call, same on all ranks
+ *     phases        3 = partition pass, then publish + wait + merge in one kernel (the normal call);
+ *                   1 = partition pass + publish only, 2 = wait + merge only (same epoch): a
+ *                   split-phase form that lets the caller put other work between the two
+ *   A peer that never arrives makes the wait time out (~2 s) and sets the status word
+ *   (b200_ctx_exchange_status) instead of hanging the device.
+ */
+int64_t b200_ctx_exchange_bytes(int world, int max_pairs, int head_size);
+int b200_paged_attention_ctx_shard(
+    void* out, float* exp_sums, float* max_logits, void* tmp_out, const void* query,
+    const void* key_cache, const void* value_cache, const int32_t* block_tables,
+    const int32_t* local_seq_lens, int num_seqs, int num_heads, int num_kv_heads, int head_size,
+    int block_size, int max_local_seq_len, int max_num_blocks_per_seq, int max_num_partitions,
+    int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride, float scale, float k_scale,
+    float v_scale, int q_dtype, int kv_dtype, void* const* exchange_bufs, int rank, int world,
+    int max_pairs, uint32_t epoch, int phases, int device, b200_stream_t stream);
+int b200_ctx_exchange_status(const void* local_buf, int world, int32_t* status, int device);
+
+/* Peer-visible device memory for the exchange buffers: plain cudaMalloc (zero-filled) exported /
+ * opened through CUDA IPC handles (64 bytes) that the host side passes between the ranks. */
+int b200_peer_alloc(void** ptr, int64_t bytes, int device);
+int b200_peer_free(void* ptr, int device);
+int b200_peer_export(const void* ptr, unsigned char* handle64, int device);
+int b200_peer_open(const unsigned char* handle64, void** ptr, int device);
+int b200_peer_close(void* ptr, int device);
+
 /* Introspection used by bench.py / tests: launch geometry the library would pick. */
 typedef struct {
   int32_t cluster_size;   /* v1: CTAs per (seq, kv-head) cooperating through DSMEM */

@@ -42,6 +42,14 @@ ABI_SYMBOLS = (
     "b200_set_attn_tuning",
     "b200_set_swap_mode",
     "b200_launch_count",
+    "b200_ctx_exchange_bytes",
+    "b200_paged_attention_ctx_shard",
+    "b200_ctx_exchange_status",
+    "b200_peer_alloc",
+    "b200_peer_free",
+    "b200_peer_export",
+    "b200_peer_open",
+    "b200_peer_close",
 )
 
 
@@ -72,6 +80,18 @@ def _load():
     lib.b200_set_swap_mode.argtypes = [ctypes.c_int]
     lib.b200_set_swap_mode.restype = None
     lib.b200_paged_attention_plan.argtypes = [ctypes.c_int] * 10 + [ctypes.POINTER(AttnPlan)]
+    lib.b200_ctx_exchange_bytes.restype = ctypes.c_int64
+    lib.b200_ctx_exchange_bytes.argtypes = [ctypes.c_int] * 3
+    vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
+    lib.b200_paged_attention_ctx_shard.argtypes = (
+        [vp] * 9 + [i32] * 8 + [i64] * 3 + [f32] * 3 + [i32] * 2 +
+        [ctypes.POINTER(vp), i32, i32, i32, ctypes.c_uint32, i32, i32, vp])
+    lib.b200_ctx_exchange_status.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_int32), i32]
+    lib.b200_peer_alloc.argtypes = [ctypes.POINTER(vp), i64, i32]
+    lib.b200_peer_free.argtypes = [vp, i32]
+    lib.b200_peer_export.argtypes = [vp, ctypes.c_char_p, i32]
+    lib.b200_peer_open.argtypes = [ctypes.c_char_p, ctypes.POINTER(vp), i32]
+    lib.b200_peer_close.argtypes = [vp, i32]
     torch.ops.load_library(BINDING_PATH)
     return lib
 

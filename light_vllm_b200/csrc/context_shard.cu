@@ -1,0 +1,261 @@
+// Context-sharded decode: ONE sequence's KV pages live on several GPUs (the
+// long-context case sequence sharding cannot cover).  Every rank runs the paged-attention
+// partition kernel over the pages it owns, then ONE kernel per rank
+//   (1) folds the rank's partitions into a single (m, l, o) triple per (seq, head),
+//   (2) all-gathers the triples by storing them straight into every peer's exchange buffer over
+//       NVLink (peer pointers from CUDA IPC; no NCCL, no host round trip),
+//   (3) signals / waits on per-CTA epoch flags (st.release.sys / ld.acquire.sys), and
+//   (4) merges the `world` triples with the v2 formula (attention_kernels.cu:565-669) into `out`.
+// Every rank ends with the full output, as the callers of paged_attention expect.
+//
+// Exchange buffer layout (identical on every rank; b200_ctx_exchange_bytes):
+//   u32   flags[world][kCtxMaxCtas]            epoch last published by (source rank, CTA)
+//   u32   status[32]                           [0] != 0: a wait timed out (peer never arrived)
+//   float data[2][world][max_pairs][D + 4]     row = {m, l, 0, 0, o[0..D)}; slot = epoch & 1
+// Two data slots suffice: a rank can only be one call ahead of its slowest peer, because call
+// n+1 cannot finish before every peer has published call n+1, which it does after reading call n.
+#include "paged_attention.cuh"
+
+#include <cstring>
+
+namespace b200 {
+
+constexpr int kCtxMaxCtas = 160;
+constexpr int kCtxMaxWorld = 16;
+constexpr int kCtxRowPad = 4;
+
+struct CtxPeers {
+  unsigned char* buf[kCtxMaxWorld];
+};
+
+__host__ __device__ inline size_t ctx_header_bytes(int world) {
+  return (((size_t)world * kCtxMaxCtas + 32) * 4 + 127) & ~(size_t)127;
+}
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(128)
+ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sums,
+                          const float* __restrict__ max_logits, const T* __restrict__ tmp_out,
+                          const int32_t* __restrict__ seq_lens, int num_heads, int head_size,
+                          int max_num_partitions, int partition_tokens, int weights_stride,
+                          int total_pairs, const __grid_constant__ CtxPeers peers, int rank,
+                          int world, int max_pairs, uint32_t epoch, int phases,
+                          long long timeout_cycles) {
+  extern __shared__ float wsm[];  // [4 warps][weights_stride]
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int row_floats = head_size + kCtxRowPad;
+  const size_t hdr = ctx_header_bytes(world);
+  const size_t slot_floats = (size_t)world * max_pairs * row_floats;
+  const size_t slot_off = (size_t)(epoch & 1u) * slot_floats;
+
+  // ---- phase 1: fold my partitions, publish the triple to every rank (incl. myself) ----
+  float* w = wsm + warp * weights_stride;
+  for (int pair = blockIdx.x * 4 + warp; (phases & 1) && pair < total_pairs; pair += gridDim.x * 4) {
+    const int seq = pair / num_heads;
+    const int seq_len = seq_lens[seq];
+    const int np = (seq_len + partition_tokens - 1) / partition_tokens;
+    const float* ml = max_logits + (int64_t)pair * max_num_partitions;
+    const float* es = exp_sums + (int64_t)pair * max_num_partitions;
+    const T* t = tmp_out + (int64_t)pair * max_num_partitions * head_size;
+    float mx = kNegInf;
+    for (int j = lane; j < np; j += 32) mx = fmaxf(mx, ml[j]);
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+    float sum = 0.f;
+    for (int j = lane; j < np; j += 32) {
+      const float r = (mx == kNegInf) ? 0.f : es[j] * expf(ml[j] - mx);
+      w[j] = r;
+      sum += r;
+    }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
+    const float inv = sum > 0.f ? __fdividef(1.f, sum) : 0.f;
+    __syncwarp();
+    const size_t row_off = slot_off + ((size_t)rank * max_pairs + pair) * row_floats;
+    for (int d0 = 2 * lane; d0 < head_size; d0 += 64) {
+      float a0 = 0.f, a1 = 0.f;
+      for (int j = 0; j < np; ++j) {
+        const float wj = w[j] * inv;
+        a0 += to_f32<T>(t[(int64_t)j * head_size + d0]) * wj;
+        a1 += to_f32<T>(t[(int64_t)j * head_size + d0 + 1]) * wj;
+      }
+      for (int r = 0; r < world; ++r) {
+        float* dst = reinterpret_cast<float*>(peers.buf[r] + hdr) + row_off;
+        *reinterpret_cast<float2*>(dst + kCtxRowPad + d0) = make_float2(a0, a1);
+      }
+    }
+    if (lane == 0) {
+      for (int r = 0; r < world; ++r) {
+        float* dst = reinterpret_cast<float*>(peers.buf[r] + hdr) + row_off;
+        *reinterpret_cast<float2*>(dst) = make_float2(mx, sum);
+      }
+    }
+    __syncwarp();  // w[] is reused by the next pair
+  }
+  __threadfence_system();
+  __syncthreads();
+  if ((phases & 1) && threadIdx.x < world) {
+    uint32_t* f = reinterpret_cast<uint32_t*>(peers.buf[threadIdx.x]) + rank * kCtxMaxCtas + blockIdx.x;
+    st_release_sys(f, epoch);
+  }
+
+  // ---- phase 2: wait for every rank's publication of this epoch, merge ----
+  if (!(phases & 2)) return;
+  unsigned char* mine = peers.buf[rank];
+  if (threadIdx.x < world) {
+    const uint32_t* f = reinterpret_cast<const uint32_t*>(mine) + threadIdx.x * kCtxMaxCtas + blockIdx.x;
+    const long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
+      if (clock64() - t0 > timeout_cycles) {
+        atomicExch(reinterpret_cast<unsigned int*>(mine) + world * kCtxMaxCtas, 1u + threadIdx.x);
+        break;
+      }
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+  const float* data = reinterpret_cast<const float*>(mine + hdr) + slot_off;
+  for (int pair = blockIdx.x * 4 + warp; pair < total_pairs; pair += gridDim.x * 4) {
+    float M = kNegInf;
+    for (int r = 0; r < world; ++r) {
+      const float2 st = __ldcg(reinterpret_cast<const float2*>(data + ((size_t)r * max_pairs + pair) * row_floats));
+      if (st.y > 0.f) M = fmaxf(M, st.x);
+    }
+    float S = 0.f;
+    for (int r = 0; r < world; ++r) {
+      const float2 st = __ldcg(reinterpret_cast<const float2*>(data + ((size_t)r * max_pairs + pair) * row_floats));
+      if (st.y > 0.f) S += st.y * expf(st.x - M);
+    }
+    const float inv = __fdividef(1.f, S + 1e-6f);
+    T* o = out + (int64_t)pair * head_size;
+    for (int d0 = 2 * lane; d0 < head_size; d0 += 64) {
+      float a0 = 0.f, a1 = 0.f;
+      for (int r = 0; r < world; ++r) {
+        const float* row = data + ((size_t)r * max_pairs + pair) * row_floats;
+        const float2 st = __ldcg(reinterpret_cast<const float2*>(row));
+        if (st.y > 0.f) {
+          const float wr = st.y * expf(st.x - M) * inv;
+          const float2 v = __ldcg(reinterpret_cast<const float2*>(row + kCtxRowPad + d0));
+          a0 += v.x * wr;
+          a1 += v.y * wr;
+        }
+      }
+      o[d0] = from_f32<T>(a0);
+      o[d0 + 1] = from_f32<T>(a1);
+    }
+  }
+}
+
+int launch_ctx_exchange(void* out, const float* exp_sums, const float* max_logits,
+                        const void* tmp_out, const int32_t* seq_lens, int num_seqs, int num_heads,
+                        int head_size, int max_num_partitions, int partition_tokens, int parts,
+                        int q_dtype, void* const* exchange_bufs, int rank, int world, int max_pairs,
+                        uint32_t epoch, int phases, cudaStream_t stream) {
+  B200_CHECK_ARG(world >= 1 && world <= kCtxMaxWorld && rank >= 0 && rank < world,
+                 "ctx_shard: bad rank/world (%d/%d)", rank, world);
+  const long long pairs = (long long)num_seqs * num_heads;
+  B200_CHECK_ARG(pairs <= max_pairs, "ctx_shard: %lld (seq, head) pairs exceed the exchange buffer's %d",
+                 pairs, max_pairs);
+  B200_CHECK_ARG(head_size % 2 == 0, "ctx_shard: odd head size");
+  B200_CHECK_ARG(phases >= 1 && phases <= 3, "ctx_shard: phases must be 1 (publish), 2 (merge) or 3");
+  CtxPeers peers{};
+  for (int r = 0; r < world; ++r) {
+    B200_CHECK_ARG(exchange_bufs && exchange_bufs[r], "ctx_shard: exchange buffer of rank %d is null", r);
+    peers.buf[r] = static_cast<unsigned char*>(exchange_bufs[r]);
+  }
+  int blocks = (int)((pairs + 3) / 4);
+  if (blocks > 148) blocks = 148;  // same on every rank (flags are per CTA); all co-resident
+  const int wstride = (parts + 3) & ~3;
+  const size_t wsmem = (size_t)4 * wstride * sizeof(float);
+  const long long timeout = 4000000000LL;  // ~2 s of SM clocks: a missing peer must not hang the GPU
+#define B200_CTX_LAUNCH(T)                                                                       \
+  ctx_exchange_merge_kernel<T><<<blocks, 128, wsmem, stream>>>(                                  \
+      static_cast<T*>(out), exp_sums, max_logits, static_cast<const T*>(tmp_out), seq_lens,     \
+      num_heads, head_size, max_num_partitions, partition_tokens, wstride, (int)pairs, peers,   \
+      rank, world, max_pairs, epoch, phases, timeout)
+  if (q_dtype == B200_DT_F16) B200_CTX_LAUNCH(__half);
+  else if (q_dtype == B200_DT_BF16) B200_CTX_LAUNCH(__nv_bfloat16);
+  else B200_CTX_LAUNCH(float);
+#undef B200_CTX_LAUNCH
+  count_launch();
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int64_t b200_ctx_exchange_bytes(int world, int max_pairs, int head_size) {
+  if (world < 1 || world > kCtxMaxWorld || max_pairs < 1 || head_size < 2) return -1;
+  return (int64_t)(ctx_header_bytes(world) +
+                   (size_t)2 * world * max_pairs * (head_size + kCtxRowPad) * sizeof(float));
+}
+
+// Peer-visible device memory.  cudaMalloc (not a pool / VMM allocation) so that it can be exported
+// with cudaIpcGetMemHandle; zero-filled so that epoch 0 flags read "nothing published".
+extern "C" int b200_peer_alloc(void** ptr, int64_t bytes, int device) {
+  B200_CHECK_ARG(ptr && bytes > 0, "peer_alloc: bad arguments");
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  B200_CUDA_OK(cudaMalloc(ptr, (size_t)bytes));
+  B200_CUDA_OK(cudaMemset(*ptr, 0, (size_t)bytes));
+  B200_CUDA_OK(cudaDeviceSynchronize());
+  return B200_OK;
+}
+
+extern "C" int b200_peer_free(void* ptr, int device) {
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  B200_CUDA_OK(cudaFree(ptr));
+  return B200_OK;
+}
+
+extern "C" int b200_peer_export(const void* ptr, unsigned char* handle64, int device) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+  B200_CHECK_ARG(ptr && handle64, "peer_export: bad arguments");
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  cudaIpcMemHandle_t h;
+  B200_CUDA_OK(cudaIpcGetMemHandle(&h, const_cast<void*>(ptr)));
+  memcpy(handle64, &h, 64);
+  return B200_OK;
+}
+
+extern "C" int b200_peer_open(const unsigned char* handle64, void** ptr, int device) {
+  B200_CHECK_ARG(ptr && handle64, "peer_open: bad arguments");
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  B200_CUDA_OK(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return B200_OK;
+}
+
+extern "C" int b200_peer_close(void* ptr, int device) {
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  B200_CUDA_OK(cudaIpcCloseMemHandle(ptr));
+  return B200_OK;
+}
+
+// Synchronous read of the exchange buffer's timeout word (tests / diagnostics; not on the hot path).
+extern "C" int b200_ctx_exchange_status(const void* local_buf, int world, int32_t* status, int device) {
+  B200_CHECK_ARG(local_buf && status, "ctx_exchange_status: bad arguments");
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  B200_CUDA_OK(cudaMemcpy(status, static_cast<const unsigned char*>(local_buf) +
+                                       (size_t)world * kCtxMaxCtas * 4,
+                          4, cudaMemcpyDeviceToHost));
+  return B200_OK;
+}

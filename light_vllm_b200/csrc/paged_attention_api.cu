@@ -20,6 +20,19 @@ int attn_f32_group_rows(int group, int head_size);
 
 constexpr int kPartitionSize = 512;  // fixed by the op contract (paged_attn.py:14)
 
+// context_shard.cu: fold this rank's partitions, exchange with the peers over NVLink, merge
+int launch_ctx_exchange(void* out, const float* exp_sums, const float* max_logits,
+                        const void* tmp_out, const int32_t* seq_lens, int num_seqs, int num_heads,
+                        int head_size, int max_num_partitions, int partition_tokens, int parts,
+                        int q_dtype, void* const* exchange_bufs, int rank, int world, int max_pairs,
+                        uint32_t epoch, int phases, cudaStream_t stream);
+struct CtxShardArgs {
+  void* const* exchange_bufs;
+  int rank, world, max_pairs;
+  uint32_t epoch;
+  int phases;  // 1 = partition pass + publish, 2 = wait + merge, 3 = both in one kernel
+};
+
 // ---------------------------------------------------------------------------------------
 // v2 merge: out = sum_j tmp_out_j * exp_sum_j * e^(m_j - m) / (sum_j exp_sum_j e^(m_j - m) + 1e-6)
 // (reference: paged_attention_v2_reduce_kernel, attention_kernels.cu:565-669, one 128-thread CTA
@@ -253,10 +266,12 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
                          int max_num_blocks_per_seq, int max_num_partitions, int64_t q_stride,
                          int64_t kv_block_stride, int64_t kv_head_stride, float scale,
                          float k_scale, float v_scale, int q_dtype, int kv_dtype,
-                         const b200_blocksparse_t* bsp, int device, cudaStream_t stream) {
+                         const b200_blocksparse_t* bsp, int device, cudaStream_t stream,
+                         const CtxShardArgs* ctx = nullptr) {
   B200_CHECK_ARG(num_seqs >= 0 && head_size > 0 && block_size > 0 && max_seq_len >= 0,
                  "paged_attention: bad sizes");
   if (num_seqs == 0) return B200_OK;
+  if (ctx) version = 2;  // context shard = v2 partition pass, partials always kept
   DeviceGuard guard(device);
   B200_CUDA_OK(guard.err);
   int dev = device;
@@ -301,7 +316,7 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
   p.gchunks = pl.gchunks;
   p.max_blocks_per_seq = max_num_blocks_per_seq;
   p.max_num_partitions = max_num_partitions;
-  const bool split_v2 = version == 2 && pl.v2_parts > 1;
+  const bool split_v2 = (version == 2 && pl.v2_parts > 1) || ctx != nullptr;
   p.partition_pages = split_v2 ? pl.v2_partition_tokens / block_size : 0;
   p.num_stages = pl.nstages;
   p.q_stride = q_stride;
@@ -324,9 +339,16 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
   B200_CHECK_ARG((long long)num_kv_heads * pl.gchunks <= 65535 && num_seqs <= 65535,
                  "paged_attention: grid too large");
   dim3 grid(splits, num_kv_heads * pl.gchunks, num_seqs);
-  rc = pl.entry.launch(p, grid, version == 2 ? 1 : pl.cluster, pl.nwarps, pl.nstages, dev, stream);
-  if (rc != B200_OK) return rc;
+  if (!(ctx && ctx->phases == 2)) {  // merge-only call of the split-phase form: partials exist already
+    rc = pl.entry.launch(p, grid, version == 2 ? 1 : pl.cluster, pl.nwarps, pl.nstages, dev, stream);
+    if (rc != B200_OK) return rc;
+  }
 
+  if (ctx)
+    return launch_ctx_exchange(out, exp_sums, max_logits, tmp_out, seq_lens, num_seqs, num_heads,
+                               head_size, max_num_partitions, pl.v2_partition_tokens, pl.v2_parts,
+                               q_dtype, ctx->exchange_bufs, ctx->rank, ctx->world, ctx->max_pairs,
+                               ctx->epoch, ctx->phases, stream);
   if (split_v2) {
     const int64_t pairs = (int64_t)num_seqs * num_heads;
     const unsigned blocks = (unsigned)((pairs + 3) / 4);
@@ -392,6 +414,24 @@ extern "C" int b200_paged_attention_v2(void* out, float* exp_sums, float* max_lo
                        max_num_partitions, q_stride, kv_block_stride, kv_head_stride, scale,
                        k_scale, v_scale, q_dtype, kv_dtype, blocksparse, device,
                        (cudaStream_t)stream);
+}
+
+extern "C" int b200_paged_attention_ctx_shard(
+    void* out, float* exp_sums, float* max_logits, void* tmp_out, const void* query,
+    const void* key_cache, const void* value_cache, const int32_t* block_tables,
+    const int32_t* local_seq_lens, int num_seqs, int num_heads, int num_kv_heads, int head_size,
+    int block_size, int max_local_seq_len, int max_num_blocks_per_seq, int max_num_partitions,
+    int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride, float scale, float k_scale,
+    float v_scale, int q_dtype, int kv_dtype, void* const* exchange_bufs, int rank, int world,
+    int max_pairs, uint32_t epoch, int phases, int device, b200_stream_t stream) {
+  B200_CHECK_ARG(exp_sums && max_logits && tmp_out, "paged_attention_ctx_shard: scratch tensors required");
+  CtxShardArgs ctx{exchange_bufs, rank, world, max_pairs, epoch, phases};
+  return run_attention(2, out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
+                       block_tables, local_seq_lens, nullptr, num_seqs, num_heads, num_kv_heads,
+                       head_size, block_size, max_local_seq_len, max_num_blocks_per_seq,
+                       max_num_partitions, q_stride, kv_block_stride, kv_head_stride, scale,
+                       k_scale, v_scale, q_dtype, kv_dtype, nullptr, device, (cudaStream_t)stream,
+                       &ctx);
 }
 
 extern "C" int b200_paged_attention_plan(int version, int num_seqs, int num_heads, int num_kv_heads,
