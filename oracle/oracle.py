@@ -179,3 +179,22 @@ def batched_rotary_embedding(positions, query, key, head_size, cos_sin_cache, is
                              cos_sin_cache_offsets):
     rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox, rot_dim,
                      cos_sin_cache_offsets)
+
+
+def context_attention_fwd(q, k, v, o, k_cache, v_cache, b_loc, b_start_loc, b_seq_len, b_ctx_len,
+                          max_input_len, alibi_slopes=None, sliding_window=None):
+    """Argument order of the reference's ``context_attention_fwd``
+    (light_vllm/decoding/backends/attention/ops/prefix_prefill.py:674-686)."""
+    for t in (q, k, v, o):
+        assert t.stride(2) == 1
+    assert b_loc.dtype == torch.int32 and b_seq_len.dtype == torch.int32 and b_ctx_len.dtype == torch.int32
+    start = b_start_loc.to(torch.int32).contiguous()
+    rc = lib().oracle_context_attention_fwd(
+        _p(q), _p(k), _p(v), _p(o), _p(k_cache), _p(v_cache), _p(b_loc), _p(start), _p(b_seq_len),
+        _p(b_ctx_len), b_seq_len.numel(), q.size(1), k.size(1), q.size(2), v_cache.size(3),
+        b_loc.size(1), _i64(q.stride(0)), _i64(q.stride(1)), _i64(k.stride(0)), _i64(k.stride(1)),
+        _i64(v.stride(0)), _i64(v.stride(1)), _i64(o.stride(0)), _i64(o.stride(1)),
+        _i64(k_cache.stride(0)), _i64(k_cache.stride(1)), _i64(v_cache.stride(0)),
+        _i64(v_cache.stride(1)), _p(alibi_slopes),
+        int(sliding_window) if sliding_window and sliding_window > 0 else 0, _DT[q.dtype])
+    assert rc == 0

@@ -453,3 +453,89 @@ int oracle_rotary_embedding(const int64_t* positions, void* query, void* key,
   }
   return 0;
 }
+
+/* ------------------------------------------------------------------ prefix prefill --- */
+/* context_attention_fwd (light_vllm/decoding/backends/attention/ops/prefix_prefill.py:674-811;
+ * kernels _fwd_kernel :13-243 and _fwd_kernel_alibi :437-672).  For sequence b, query token i
+ * (position ctx_len + i, packed at row start_loc[b] + i) attends the ctx_len cached tokens read
+ * through the block table (K layout [NB,KH,D/x,BS,x] :112-117, V layout [NB,KH,D,BS] :119-123,
+ * no mask :125-131) and the new tokens j <= i read from the packed k/v tensors (causal mask
+ * :205-207).  sm_scale = 1/sqrt(D) (:702).  Sliding window: keys with pos_q - pos_k >= window get
+ * the logit -10000 (:132-148, :208-211).  ALiBi: bias slope * (pos_k - pos_q), entries with a
+ * positive bias are masked (:551-557, :622-628).  The Triton kernel runs the softmax online over
+ * 128-token tiles with fp32 statistics and rounds P to the value dtype before P.V (:170,:236);
+ * this restatement computes the same softmax in one pass (fp32 logits, P rounded to T, fp32
+ * accumulation) -- the tile order only changes fp32 summation order.
+ * Pinned by tests/golden/prefix.pt = outputs of the reference kernel itself (Triton interpreter,
+ * tests/golden/make_golden_prefix.py).  start_loc: int32 [B]. */
+int oracle_context_attention_fwd(const void* q, const void* k, const void* v, void* out,
+                                 const void* k_cache, const void* v_cache,
+                                 const int32_t* block_tables, const int32_t* start_loc,
+                                 const int32_t* seq_lens, const int32_t* ctx_lens, int num_seqs,
+                                 int num_heads, int num_kv_heads, int head_size, int block_size,
+                                 int max_blocks_per_seq, int64_t q_stride0, int64_t q_stride1,
+                                 int64_t k_stride0, int64_t k_stride1, int64_t v_stride0,
+                                 int64_t v_stride1, int64_t o_stride0, int64_t o_stride1,
+                                 int64_t kc_block_stride, int64_t kc_head_stride,
+                                 int64_t vc_block_stride, int64_t vc_head_stride,
+                                 const float* alibi_slopes, int sliding_window, int dt) {
+  const int D = head_size, BS = block_size;
+  const int x = 16 / elem_size(dt);
+  const float sm_scale = 1.0f / sqrtf((float)D);
+  const int group = num_heads / num_kv_heads;
+  int rc = 0;
+#pragma omp parallel for collapse(2) schedule(dynamic)
+  for (int b = 0; b < num_seqs; ++b) {
+    for (int h = 0; h < num_heads; ++h) {
+      const int ctx = ctx_lens[b], qlen = seq_lens[b] - ctx_lens[b];
+      if (qlen <= 0) continue;
+      const int kvh = h / group;
+      const int32_t* bt = block_tables + (int64_t)b * max_blocks_per_seq;
+      float* logits = (float*)malloc(sizeof(float) * (size_t)(ctx + qlen));
+      float* acc = (float*)malloc(sizeof(float) * (size_t)D);
+      if (!logits || !acc) { rc = 1; free(logits); free(acc); continue; }
+      const float slope = alibi_slopes ? alibi_slopes[h] : 0.f;
+      for (int i = 0; i < qlen; ++i) {
+        const int64_t qrow = (int64_t)(start_loc[b] + i) * q_stride0 + (int64_t)h * q_stride1;
+        const int pos_q = ctx + i, n = ctx + i + 1;
+        float mx = -INFINITY;
+        for (int t = 0; t < n; ++t) {
+          float dot = 0.f;
+          if (t < ctx) {
+            const int64_t base = (int64_t)bt[t / BS] * kc_block_stride + (int64_t)kvh * kc_head_stride;
+            for (int d = 0; d < D; ++d)
+              dot += load_elem(q, qrow + d, dt) *
+                     load_elem(k_cache, base + (int64_t)(d / x) * BS * x + (int64_t)(t % BS) * x + d % x, dt);
+          } else {
+            const int64_t krow = (int64_t)(start_loc[b] + t - ctx) * k_stride0 + (int64_t)kvh * k_stride1;
+            for (int d = 0; d < D; ++d) dot += load_elem(q, qrow + d, dt) * load_elem(k, krow + d, dt);
+          }
+          float s = dot * sm_scale;
+          if (alibi_slopes) s += slope * (float)(t - pos_q);
+          if (sliding_window > 0 && pos_q - t >= sliding_window) s = -10000.f;
+          logits[t] = s;
+          mx = fmaxf(mx, s);
+        }
+        float sum = 0.f;
+        for (int t = 0; t < n; ++t) { logits[t] = expf(logits[t] - mx); sum += logits[t]; }
+        for (int d = 0; d < D; ++d) acc[d] = 0.f;
+        for (int t = 0; t < n; ++t) {
+          const float p = round_to(logits[t] / sum, dt);
+          if (p == 0.f) continue;
+          if (t < ctx) {
+            const int64_t base = (int64_t)bt[t / BS] * vc_block_stride + (int64_t)kvh * vc_head_stride;
+            for (int d = 0; d < D; ++d) acc[d] += p * load_elem(v_cache, base + (int64_t)d * BS + t % BS, dt);
+          } else {
+            const int64_t vrow = (int64_t)(start_loc[b] + t - ctx) * v_stride0 + (int64_t)kvh * v_stride1;
+            for (int d = 0; d < D; ++d) acc[d] += p * load_elem(v, vrow + d, dt);
+          }
+        }
+        const int64_t orow = (int64_t)(start_loc[b] + i) * o_stride0 + (int64_t)h * o_stride1;
+        for (int d = 0; d < D; ++d) store_elem(out, orow + d, dt, acc[d]);
+      }
+      free(logits);
+      free(acc);
+    }
+  }
+  return rc;
+}
