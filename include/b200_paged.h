@@ -220,6 +220,33 @@ int64_t b200_get_device_attribute(int64_t attribute, int64_t device_id);
 int64_t b200_get_max_shared_memory_per_block_device_attribute(int64_t device_id);
 
 /*
+ * context_attention_fwd — replaces the Triton kernels behind PagedAttention.forward_prefix
+ *   (light_vllm/decoding/backends/attention/ops/prefix_prefill.py:674-811; caller
+ *   ops/paged_attn.py:193-225): prefill of new tokens whose sequence already has ctx_len tokens in
+ *   the paged cache (prefix-cache hit, chunked prefill).
+ *     q / out      [num_tokens, num_heads, head_size]     T (fp16 | bf16), strides *_stride0/1
+ *     k / v        [num_tokens, num_kv_heads, head_size]  T: the NEW tokens, packed per sequence
+ *     key_cache    [num_blocks, num_kv_heads, head_size/x, block_size, x], value_cache
+ *                  [num_blocks, num_kv_heads, head_size, block_size]  T (the reference kernel has no
+ *                  fp8 path); only the first ctx_len tokens of each sequence are read from them
+ *     block_tables [num_seqs, max_blocks_per_seq] int32; start_loc [num_seqs] int32 (first packed
+ *                  row of each sequence); seq_lens = ctx_lens + query length, ctx_lens: int32
+ *     alibi_slopes [num_heads] float32 or NULL; sliding_window <= 0 disables the window (ignored
+ *                  with ALiBi, as in the reference dispatch :713-811)
+ *     scale        the reference fixes 1/sqrt(head_size) (:702); passed explicitly here
+ *   Query token i attends all ctx_len cached tokens and new tokens j <= i.
+ */
+int b200_context_attention_fwd(
+    const void* q, const void* k, const void* v, void* out, const void* key_cache,
+    const void* value_cache, const int32_t* block_tables, const int32_t* start_loc,
+    const int32_t* seq_lens, const int32_t* ctx_lens, int num_seqs, int num_heads, int num_kv_heads,
+    int head_size, int block_size, int max_blocks_per_seq, int max_query_len, int64_t q_stride0,
+    int64_t q_stride1, int64_t k_stride0, int64_t k_stride1, int64_t v_stride0, int64_t v_stride1,
+    int64_t o_stride0, int64_t o_stride1, int64_t kc_block_stride, int64_t kc_head_stride,
+    int64_t vc_block_stride, int64_t vc_head_stride, const float* alibi_slopes, int sliding_window,
+    float scale, int dtype, int device, b200_stream_t stream);
+
+/*
  * Context-sharded decode (one sequence whose KV pages are spread over several
  * GPUs).  No reference twin: the reference keeps a sequence's pool on one device; the merge is
  * the reference's own v2 formula (attention_kernels.cu:565-669) applied across ranks.

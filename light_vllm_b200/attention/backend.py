@@ -9,7 +9,8 @@ backend is FlashAttention (decoding/backends/attention/backends/flash_attn.py:20
   * swap / copy   -> swap_blocks / copy_blocks
 through ``light_vllm_b200._custom_ops``.  Prompt (prefill) tokens without a cached prefix go
 through torch SDPA -- a library call outside the decode hot path, as flash_attn_varlen_func is in
-the reference; prefix-cached prefill is a "next" row.
+the reference; prefix-cached / chunked prefill runs the sm_100a ``context_attention_fwd`` kernel
+(SURVEY.md 8f rank 4).
 """
 from dataclasses import dataclass
 from typing import Any, Dict, List, Optional, Tuple, Type
@@ -303,9 +304,21 @@ class PagedB200AttentionImpl(DecodeOnlyAttentionImpl):
                 output[:n_prefill] = self._prefill(query[:n_prefill], key[:n_prefill],
                                                    value[:n_prefill], prefill_meta)
             else:
-                raise NotImplementedError(
-                    "prefix-cached / chunked prefill over the paged cache is not built yet "
-                    "(reference: PagedAttention.forward_prefix, paged_attn.py:193-225)")
+                # prefix-cache hit / chunked prefill: new tokens attend the cached context through
+                # the block table plus themselves causally (reference: xformers.py / rocm / ipex
+                # backends -> PagedAttention.forward_prefix, paged_attn.py:193-225)
+                if self.kv_cache_dtype != "auto":
+                    raise NotImplementedError(
+                        "prefix-cached prefill reads the cache in the query dtype; the reference "
+                        "kernel (prefix_prefill.py) has no fp8 path either")
+                alibi = self.alibi_slopes
+                if alibi is not None and alibi.device != query.device:
+                    alibi = self.alibi_slopes = alibi.to(query.device)
+                output[:n_prefill] = PagedAttention.forward_prefix(
+                    query[:n_prefill], key[:n_prefill], value[:n_prefill], key_cache, value_cache,
+                    prefill_meta.block_tables, prefill_meta.query_start_loc,
+                    prefill_meta.seq_lens_tensor, prefill_meta.context_lens_tensor,
+                    prefill_meta.max_query_len, alibi, self.sliding_window)
         if decode_meta is not None:
             output[n_prefill:] = self._decode(query[n_prefill:], key_cache, value_cache,
                                               decode_meta, k_scale, v_scale)

@@ -11,6 +11,7 @@ from typing import Dict, List, Optional, Tuple
 import torch
 
 from light_vllm_b200 import _custom_ops as ops
+from light_vllm_b200.attention.prefix_prefill import context_attention_fwd
 
 # Fixed by the op contract: partition size of paged_attention_v2 (paged_attn.py:14).
 _PARTITION_SIZE = 512
@@ -107,6 +108,21 @@ class PagedAttention:
                                    value_cache, num_kv_heads, scale, block_tables, seq_lens,
                                    block_size, max_seq_len, alibi_slopes, kv_cache_dtype, k_scale,
                                    v_scale, *tail)
+        return output
+
+    @staticmethod
+    def forward_prefix(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                       key_cache: torch.Tensor, value_cache: torch.Tensor,
+                       block_tables: torch.Tensor, query_start_loc: torch.Tensor,
+                       seq_lens_tensor: torch.Tensor, context_lens: torch.Tensor,
+                       max_query_len: int, alibi_slopes: Optional[torch.Tensor],
+                       sliding_window: Optional[int]) -> torch.Tensor:
+        """Prefill of new tokens over a cached prefix (reference: paged_attn.py:193-225)."""
+        output = torch.empty_like(query)
+        # query_start_loc is (batch_size + 1,)
+        context_attention_fwd(query, key, value, output, key_cache, value_cache, block_tables,
+                              query_start_loc[:-1], seq_lens_tensor, context_lens, max_query_len,
+                              alibi_slopes, sliding_window)
         return output
 
     @staticmethod

@@ -1,0 +1,47 @@
+"""Prefill over a cached prefix: the reference's ``context_attention_fwd`` entry point
+(light_vllm/decoding/backends/attention/ops/prefix_prefill.py:674-686), same name, argument order
+and meaning, served by the sm_100a kernel behind ``b200_context_attention_fwd``
+(``csrc/prefix_prefill.cu``) instead of Triton.  CUDA tensors only; there is no fallback."""
+from typing import Optional
+
+import torch
+
+from .. import _lib
+
+
+def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: torch.Tensor,
+                          k_cache: torch.Tensor, v_cache: torch.Tensor, b_loc: torch.Tensor,
+                          b_start_loc: torch.Tensor, b_seq_len: torch.Tensor,
+                          b_ctx_len: torch.Tensor, max_input_len: int,
+                          alibi_slopes: Optional[torch.Tensor] = None,
+                          sliding_window: Optional[int] = None) -> None:
+    if not q.is_cuda:
+        raise RuntimeError("context_attention_fwd: CUDA tensors required (no CPU implementation)")
+    if q.dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError(f"Unsupported data type: context_attention_fwd runs fp16 / bf16, got {q.dtype}")
+    if k_cache.dtype != q.dtype or v_cache.dtype != q.dtype:
+        raise RuntimeError("context_attention_fwd: the cache must hold the query dtype "
+                           "(the reference kernel has no fp8 path)")
+    for t in (q, k, v, o):
+        assert t.dim() == 3 and t.stride(2) == 1
+    Lq, Lk, Lv = q.shape[-1], k.shape[-1], v.shape[-1]
+    assert Lq == Lk and Lk == Lv  # prefix_prefill.py:697-698
+    i32 = lambda t: t if t.dtype == torch.int32 else t.to(torch.int32)  # noqa: E731
+    b_loc, b_start_loc, b_seq_len, b_ctx_len = (i32(b_loc), i32(b_start_loc).contiguous(),
+                                                i32(b_seq_len).contiguous(), i32(b_ctx_len).contiguous())
+    assert b_loc.stride(1) == 1
+    if alibi_slopes is not None:
+        alibi_slopes = alibi_slopes.to(torch.float32).contiguous()
+    import ctypes
+    rc = _lib.lib.b200_context_attention_fwd(
+        q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+        b_loc.data_ptr(), b_start_loc.data_ptr(), b_seq_len.data_ptr(), b_ctx_len.data_ptr(),
+        b_seq_len.shape[0], q.shape[1], k.shape[1], Lq, v_cache.shape[3], b_loc.stride(0),
+        int(max_input_len), q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
+        o.stride(0), o.stride(1), k_cache.stride(0), k_cache.stride(1), v_cache.stride(0),
+        v_cache.stride(1), alibi_slopes.data_ptr() if alibi_slopes is not None else None,
+        int(sliding_window) if sliding_window and sliding_window > 0 else 0,
+        ctypes.c_float(1.0 / (Lq ** 0.5)), _lib._DT[q.dtype], q.device.index,
+        torch.cuda.current_stream(q.device).cuda_stream)
+    if rc != 0:
+        raise RuntimeError(_lib.last_error())

@@ -124,14 +124,20 @@ __device__ __forceinline__ int page_token(int nt, int qq, int e) {
 
 // One KV page (BS tokens) against the warp's q-group: S = QK^T, online softmax, O += P V.
 // PLAIN: no ALiBi and no blocksparse mask (the common case) -- the logit is just s * scale.
-template <typename T, int D, int BS, int KV, int GROWS, bool TAIL, bool PLAIN>
-__device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
-                                             const uint32_t (&qa)[(D + 15) / 16][GROWS / 4],
-                                             float (&o)[D / 8][GROWS / 4], float (&m)[GROWS / 8],
-                                             float (&l)[GROWS / 8], int lane, int valid,
-                                             float scale_log2, const float (&slope)[GROWS / 8],
-                                             float tok_rel0,  // (first token of page) - seq_len + 1
-                                             const bool (&row_on)[GROWS / 8]) {
+// ROWB (prefix prefill): every row has its own window of visible tokens [row_lo, row_hi) inside the
+// page (causal frontier / sliding window) and its own ALiBi origin row_rel0 = (first token of the
+// page) - (the row's query position); decode rows all share `valid` and `tok_rel0`.
+template <typename T, int D, int BS, int KV, int GROWS, bool TAIL, bool PLAIN, bool ROWB>
+__device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem,
+                                                const uint32_t (&qa)[(D + 15) / 16][GROWS / 4],
+                                                float (&o)[D / 8][GROWS / 4], float (&m)[GROWS / 8],
+                                                float (&l)[GROWS / 8], int lane, int valid,
+                                                float scale_log2, const float (&slope)[GROWS / 8],
+                                                float tok_rel0,  // (first token of page) - seq_len + 1
+                                                const bool (&row_on)[GROWS / 8],
+                                                const int (&row_lo)[GROWS / 8],
+                                                const int (&row_hi)[GROWS / 8],
+                                                const float (&row_rel0)[GROWS / 8]) {
   using MT = typename MmaType<T, KV>::type;
   constexpr int ES = KvTraits<KV>::ES;
   constexpr int KS = (D + 15) / 16;  // k-steps over head dim
@@ -207,9 +213,11 @@ __device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
       for (int e = 0; e < 2; ++e) {
         const int t = page_token<KV, BS>(nt, q4, e);  // token within page
         float x = s[nt][2 * rs + e] * scale_log2;
-        if constexpr (!PLAIN) x += slope[rs] * (tok_rel0 + (float)t);
+        if constexpr (!PLAIN) x += slope[rs] * ((ROWB ? row_rel0[rs] : tok_rel0) + (float)t);
         if (TAIL && t >= valid) x = kNegInf;
-        if constexpr (!PLAIN) {
+        if constexpr (ROWB) {
+          if (t < row_lo[rs] || t >= row_hi[rs]) x = kNegInf;
+        } else if constexpr (!PLAIN) {
           if (!row_on[rs]) x = kNegInf;
         }
         s[nt][2 * rs + e] = x;
@@ -362,6 +370,21 @@ __device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
     }
   }
   (void)ES;
+}
+
+// Decode form: uniform tail, optional per-row on/off (blocksparse).
+template <typename T, int D, int BS, int KV, int GROWS, bool TAIL, bool PLAIN>
+__device__ __forceinline__ void process_page(uint32_t k_smem, uint32_t v_smem,
+                                             const uint32_t (&qa)[(D + 15) / 16][GROWS / 4],
+                                             float (&o)[D / 8][GROWS / 4], float (&m)[GROWS / 8],
+                                             float (&l)[GROWS / 8], int lane, int valid,
+                                             float scale_log2, const float (&slope)[GROWS / 8],
+                                             float tok_rel0, const bool (&row_on)[GROWS / 8]) {
+  const int zi[GROWS / 8] = {};
+  const float zf[GROWS / 8] = {};
+  process_page_ex<T, D, BS, KV, GROWS, TAIL, PLAIN, false>(k_smem, v_smem, qa, o, m, l, lane, valid,
+                                                           scale_log2, slope, tok_rel0, row_on, zi,
+                                                           zi, zf);
 }
 
 }  // namespace b200

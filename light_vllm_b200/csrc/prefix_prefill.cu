@@ -1,0 +1,406 @@
+// Prefix / chunked-prefill attention over the paged cache: replaces context_attention_fwd
+// (light_vllm/decoding/backends/attention/ops/prefix_prefill.py:674-811, Triton kernels :13-243 and
+// :437-672) behind PagedAttention.forward_prefix (ops/paged_attn.py:193-225).
+//
+// Query token i of sequence b (position ctx_len + i) attends (1) the ctx_len tokens already in the
+// paged cache, unmasked, and (2) the new tokens j <= i, read from the packed k/v tensors.
+//
+// One 4-warp CTA owns (sequence, KV head, tile of query tokens).  The M dimension of the MMAs is
+// (query token, q-head of the GQA group): row r = token r / G, head r % G, 16 (or 8) rows per warp,
+// so all q-heads of a group share ONE pass over K/V (the reference launches one program per
+// q-head).  Phase 1 streams the context pages through a CTA-wide ring of bulk copies (TMA engine,
+// full/empty mbarriers, no CTA barrier); every warp runs process_page_ex() on the page for its
+// rows.  Phase 2 stages BS-token slices of the new k/v into the same page layouts in shared memory
+// (registers prefetched one slice ahead) and applies the causal frontier per row.  Online softmax
+// in the exp2 domain, fp32 statistics and accumulation, mma.sync m16n8k16 (legacy tensor path).
+#include "paged_attention.cuh"
+
+#include <atomic>
+
+namespace b200 {
+
+struct PrefixParams {
+  const void *q, *k, *v;
+  void* out;
+  const void *k_cache, *v_cache;
+  const int32_t *block_tables, *start_loc, *seq_lens, *ctx_lens;
+  const float* alibi_slopes;
+  int num_heads, num_kv_heads, group, max_blocks_per_seq, sliding_window, tok_tile, num_stages;
+  int64_t q_s0, q_s1, k_s0, k_s1, v_s0, v_s1, o_s0, o_s1, kc_bs, kc_hs, vc_bs, vc_hs;
+  float scale_log2;
+};
+
+constexpr int kPrefixWarps = 4;
+
+template <typename T, int D, int BS, int GROWS, bool PLAIN>
+__global__ void __launch_bounds__(kPrefixWarps * 32)
+context_attention_kernel(const __grid_constant__ PrefixParams p) {
+  constexpr int KV = B200_KV_AUTO;
+  constexpr int PAGE_BYTES = D * BS * 2;
+  constexpr int STAGE_BYTES = 2 * PAGE_BYTES;
+  constexpr int RS = GROWS / 8;
+  constexpr int NDT = D / 8;
+  constexpr int KS = (D + 15) / 16;
+  constexpr int NTHREADS = kPrefixWarps * 32;
+  constexpr int VEC_PER_PAGE = BS * NDT;                           // 16-byte vectors in a K (or V) slice
+  constexpr int VPT = (VEC_PER_PAGE + NTHREADS - 1) / NTHREADS;    // per thread
+
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int NS = p.num_stages;
+
+  const int seq = blockIdx.z;
+  const int kvh = blockIdx.y;
+  const int ctx = p.ctx_lens[seq];
+  const int qlen = p.seq_lens[seq] - ctx;
+  const int m0 = blockIdx.x * p.tok_tile;  // first query token of this CTA
+  if (m0 >= qlen) return;
+  const int64_t start = p.start_loc[seq];
+  const int G = p.group;
+  const int tile_tokens = min(p.tok_tile, qlen - m0);
+  const int W = p.sliding_window;
+
+  unsigned char* ring = smem;  // [NS stages][K page | V page], then the mbarriers, then slack
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)NS * STAGE_BYTES);
+  const uint32_t ring_u32 = smem_u32(ring);
+  const uint32_t full_u32 = smem_u32(bars);
+  const uint32_t empty_u32 = full_u32 + 8 * NS;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NS; ++s) {
+      mbar_init(full_u32 + 8 * s, 1);
+      mbar_init(empty_u32 + 8 * s, kPrefixWarps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  // ---- rows of this lane: (token, head) pairs ----
+  const int g = lane >> 2, q4 = lane & 3;
+  int row_tok[RS];    // query index within the sequence (m0 + ...), or -1 for a padding row
+  int row_head[RS];
+  float slope[RS];
+#pragma unroll
+  for (int rs = 0; rs < RS; ++rs) {
+    const int r = warp * GROWS + g + 8 * rs;
+    const int ti = r / G;
+    const bool on = ti < tile_tokens;
+    row_tok[rs] = on ? m0 + ti : -1;
+    row_head[rs] = kvh * G + (r - ti * G);
+    slope[rs] = (!PLAIN && on && p.alibi_slopes) ? p.alibi_slopes[row_head[rs]] * 1.4426950408889634f : 0.f;
+  }
+  // warp-uniform range of query indices this warp holds (padding rows excluded)
+  const int w_r0 = warp * GROWS, w_r1 = w_r0 + GROWS - 1;
+  const int w_tok_lo = m0 + w_r0 / G;
+  const int w_tok_hi = m0 + min(w_r1 / G, tile_tokens - 1);
+  const bool warp_on = (w_r0 / G) < tile_tokens;
+
+  // ---- Q fragments ----
+  uint32_t qa[KS][GROWS / 4];
+#pragma unroll
+  for (int rs = 0; rs < RS; ++rs) {
+    const bool on = row_tok[rs] >= 0;
+    const T* qrow = static_cast<const T*>(p.q) + (start + (on ? row_tok[rs] : 0)) * p.q_s0 +
+                    (int64_t)row_head[rs] * p.q_s1;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      uint32_t lo = 0u, hi = 0u;
+      const int d0 = 16 * ks + 2 * q4;
+      if (on) {
+        if (d0 < D) lo = *reinterpret_cast<const uint32_t*>(qrow + d0);
+        if (d0 + 8 < D) hi = *reinterpret_cast<const uint32_t*>(qrow + d0 + 8);
+      }
+      qa[ks][2 * rs] = lo;
+      qa[ks][2 * rs + 1] = hi;
+    }
+  }
+  float o[NDT][GROWS / 4];
+#pragma unroll
+  for (int j = 0; j < NDT; ++j)
+#pragma unroll
+    for (int e = 0; e < GROWS / 4; ++e) o[j][e] = 0.f;
+  float m[RS], l[RS];
+#pragma unroll
+  for (int rs = 0; rs < RS; ++rs) {
+    m[rs] = kNegInf;
+    l[rs] = 0.f;
+  }
+  bool row_on[RS];
+#pragma unroll
+  for (int rs = 0; rs < RS; ++rs) row_on[rs] = true;
+
+  // =========================== phase 1: cached context ===========================
+  {
+    const int n_pages = (ctx + BS - 1) / BS;
+    int page0 = 0;
+    if (W > 0) page0 = max(0, ctx + m0 - W + 1) / BS;  // nothing older is visible to any row
+    const int n = max(0, n_pages - page0);
+    const int32_t* bt = p.block_tables + (int64_t)seq * p.max_blocks_per_seq + page0;
+    const unsigned char* kbase =
+        static_cast<const unsigned char*>(p.k_cache) + (int64_t)kvh * p.kc_hs * 2;
+    const unsigned char* vbase =
+        static_cast<const unsigned char*>(p.v_cache) + (int64_t)kvh * p.vc_hs * 2;
+    const uint64_t policy = l2_policy_evict_first();
+    int win0 = 0;
+    int tbl = (warp == 0 && lane < n) ? bt[lane] : 0;
+    auto issue = [&](int i) {  // warp 0, all lanes: page i -> stage i % NS
+      if (i >= win0 + 32) {
+        win0 += 32;
+        tbl = (win0 + lane < n) ? bt[win0 + lane] : 0;
+      }
+      const int64_t blk = __shfl_sync(0xffffffffu, tbl, i - win0);
+      if (elect_one()) {
+        const int s = i % NS;
+        const uint32_t bar = full_u32 + 8 * s;
+        const uint32_t dst = ring_u32 + (uint32_t)s * STAGE_BYTES;
+        mbar_arrive_expect_tx(bar, STAGE_BYTES);
+        bulk_g2s(dst, kbase + blk * p.kc_bs * 2, PAGE_BYTES, bar, policy);
+        bulk_g2s(dst + PAGE_BYTES, vbase + blk * p.vc_bs * 2, PAGE_BYTES, bar, policy);
+      }
+    };
+    if (warp == 0) {
+      const int pre = min(NS, n);
+      for (int i = 0; i < pre; ++i) issue(i);
+    }
+    for (int i = 0; i < n; ++i) {
+      const int s = i % NS;
+      if (warp == 0 && i >= 1 && i - 1 + NS < n) {  // refill the stage every warp left one page ago
+        mbar_wait(empty_u32 + 8 * ((i - 1) % NS), (uint32_t)(((i - 1) / NS) & 1));
+        issue(i - 1 + NS);
+      }
+      mbar_wait(full_u32 + 8 * s, (uint32_t)((i / NS) & 1));
+      if (warp_on) {
+        const int tok0 = (page0 + i) * BS;
+        const uint32_t ksm = ring_u32 + (uint32_t)s * STAGE_BYTES;
+        int row_lo[RS], row_hi[RS];
+        float row_rel0[RS];
+#pragma unroll
+        for (int rs = 0; rs < RS; ++rs) {
+          const int pos_q = ctx + max(row_tok[rs], 0);
+          row_lo[rs] = W > 0 ? pos_q - W + 1 - tok0 : 0;
+          row_hi[rs] = BS;
+          row_rel0[rs] = (float)(tok0 - pos_q);
+        }
+        const bool tail = tok0 + BS > ctx;
+        const bool windowed = W > 0 && (ctx + w_tok_hi - W + 1 > tok0);
+        if (tail)
+          process_page_ex<T, D, BS, KV, GROWS, true, PLAIN, true>(
+              ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, ctx - tok0, p.scale_log2, slope, 0.f, row_on,
+              row_lo, row_hi, row_rel0);
+        else if (windowed || !PLAIN)
+          process_page_ex<T, D, BS, KV, GROWS, false, PLAIN, true>(
+              ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS, p.scale_log2, slope, 0.f, row_on, row_lo,
+              row_hi, row_rel0);
+        else
+          process_page_ex<T, D, BS, KV, GROWS, false, true, false>(
+              ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS, p.scale_log2, slope, 0.f, row_on, row_lo,
+              row_hi, row_rel0);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty_u32 + 8 * s);
+    }
+  }
+  __syncthreads();  // the ring becomes the staging area of phase 2
+
+  // =========================== phase 2: new tokens (causal) ===========================
+  {
+    const int last_tok = m0 + tile_tokens - 1;  // newest query of this CTA: keys j <= last_tok
+    int slice0 = 0;
+    if (W > 0) slice0 = max(0, m0 - W + 1) / BS;
+    const int n = last_tok / BS + 1 - slice0;
+    const T* kg = static_cast<const T*>(p.k) + (int64_t)kvh * p.k_s1;
+    const T* vg = static_cast<const T*>(p.v) + (int64_t)kvh * p.v_s1;
+    uint4 kr[VPT], vr[VPT];
+    auto fetch = [&](int i) {  // slice i (tokens (slice0+i)*BS ..) -> registers
+      const int t0 = (slice0 + i) * BS;
+#pragma unroll
+      for (int u = 0; u < VPT; ++u) {
+        const int idx = threadIdx.x + u * NTHREADS;
+        const int t = idx % BS, c = idx / BS;
+        kr[u] = make_uint4(0u, 0u, 0u, 0u);
+        vr[u] = make_uint4(0u, 0u, 0u, 0u);
+        if (idx < VEC_PER_PAGE && t0 + t < qlen) {
+          kr[u] = *reinterpret_cast<const uint4*>(kg + (start + t0 + t) * p.k_s0 + c * 8);
+          vr[u] = *reinterpret_cast<const uint4*>(vg + (start + t0 + t) * p.v_s0 + c * 8);
+        }
+      }
+    };
+    auto stash = [&](int buf) {  // registers -> K page [D/8][BS][8], V page [D][BS]
+      unsigned char* kd = ring + (size_t)buf * STAGE_BYTES;
+      unsigned char* vd = kd + PAGE_BYTES;
+#pragma unroll
+      for (int u = 0; u < VPT; ++u) {
+        const int idx = threadIdx.x + u * NTHREADS;
+        const int t = idx % BS, c = idx / BS;
+        if (idx < VEC_PER_PAGE) {
+          *reinterpret_cast<uint4*>(kd + (size_t)(c * BS + t) * 16) = kr[u];
+          const uint16_t* e = reinterpret_cast<const uint16_t*>(&vr[u]);
+#pragma unroll
+          for (int x = 0; x < 8; ++x)
+            *reinterpret_cast<uint16_t*>(vd + (size_t)((c * 8 + x) * BS + t) * 2) = e[x];
+        }
+      }
+    };
+    if (n > 0) {
+      fetch(0);
+      stash(0);
+    }
+    __syncthreads();
+    for (int i = 0; i < n; ++i) {
+      if (i + 1 < n) fetch(i + 1);
+      const int t0 = (slice0 + i) * BS;
+      if (warp_on && t0 <= w_tok_hi) {
+        const uint32_t ksm = ring_u32 + (uint32_t)(i & 1) * STAGE_BYTES;
+        int row_lo[RS], row_hi[RS];
+        float row_rel0[RS];
+#pragma unroll
+        for (int rs = 0; rs < RS; ++rs) {
+          const int iq = max(row_tok[rs], 0);
+          row_lo[rs] = W > 0 ? iq - W + 1 - t0 : 0;
+          row_hi[rs] = iq - t0 + 1;  // causal: key j <= query i
+          row_rel0[rs] = (float)(t0 - iq);
+        }
+        const bool frontier = t0 + BS - 1 > w_tok_lo;
+        const bool windowed = W > 0 && (w_tok_hi - W + 1 > t0);
+        if (frontier || windowed || !PLAIN)
+          process_page_ex<T, D, BS, KV, GROWS, false, PLAIN, true>(
+              ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS, p.scale_log2, slope, 0.f, row_on, row_lo,
+              row_hi, row_rel0);
+        else
+          process_page_ex<T, D, BS, KV, GROWS, false, true, false>(
+              ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS, p.scale_log2, slope, 0.f, row_on, row_lo,
+              row_hi, row_rel0);
+      }
+      if (i + 1 < n) stash((i + 1) & 1);
+      __syncthreads();
+    }
+  }
+
+  // ---- epilogue: normalise and store (the reference divides by the plain sum, :160-166) ----
+#pragma unroll
+  for (int rs = 0; rs < RS; ++rs) {
+    float L = l[rs];
+    L += __shfl_xor_sync(0xffffffffu, L, 1);
+    L += __shfl_xor_sync(0xffffffffu, L, 2);
+    if (row_tok[rs] < 0) continue;
+    const float inv = L > 0.f ? 1.f / L : 0.f;
+    T* orow = static_cast<T*>(p.out) + (start + row_tok[rs]) * p.o_s0 + (int64_t)row_head[rs] * p.o_s1;
+#pragma unroll
+    for (int j = 0; j < NDT; ++j) {
+      const uint32_t packed = MmaOp<T>::pack(o[j][2 * rs] * inv, o[j][2 * rs + 1] * inv);
+      *reinterpret_cast<uint32_t*>(orow + 8 * j + 2 * q4) = packed;
+    }
+  }
+}
+
+namespace {
+
+template <int D, int BS>
+constexpr size_t prefix_smem(int ns) {
+  // + 1 KiB slack: ldmatrix.x4 over an odd number of 8-wide d chunks (head 120) reads past the page
+  return (size_t)ns * 2 * D * BS * 2 + (size_t)ns * 16 + 1024;
+}
+
+template <typename T, int D, int BS>
+int launch_prefix(PrefixParams& p, int num_seqs, int max_query_len, int device, cudaStream_t stream) {
+  constexpr int GROWS = D <= 128 ? 16 : 8;
+  constexpr int ROWS = kPrefixWarps * GROWS;
+  B200_CHECK_ARG(p.group <= ROWS, "context_attention_fwd: %d q-heads per kv-head exceed the %d-row tile",
+                 p.group, ROWS);
+  p.tok_tile = ROWS / p.group;
+  int ns = 4;
+  while (ns > 2 && prefix_smem<D, BS>(ns) > (size_t)100 * 1024) --ns;
+  p.num_stages = ns;
+  const size_t smem = prefix_smem<D, BS>(ns);
+  const bool plain = p.alibi_slopes == nullptr;
+  auto kern = plain ? context_attention_kernel<T, D, BS, GROWS, true>
+                    : context_attention_kernel<T, D, BS, GROWS, false>;
+  static std::atomic<int> configured[2][64];
+  const int slot = device & 63;
+  if (!configured[plain][slot].load(std::memory_order_acquire)) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    configured[plain][slot].store(1, std::memory_order_release);
+  }
+  const int tiles = (max_query_len + p.tok_tile - 1) / p.tok_tile;
+  B200_CHECK_ARG(p.num_kv_heads <= 65535 && num_seqs <= 65535, "context_attention_fwd: grid too large");
+  // longest tiles first would need the per-sequence lengths on the host; x = tile keeps the CTAs of
+  // one (sequence, kv head) adjacent so that they share the context pages in L2
+  dim3 grid(tiles, p.num_kv_heads, num_seqs);
+  kern<<<grid, kPrefixWarps * 32, smem, stream>>>(p);
+  count_launch();
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+template <typename T>
+int dispatch_prefix(PrefixParams& p, int head_size, int block_size, int num_seqs, int max_query_len,
+                    int device, cudaStream_t stream) {
+#define B200_PFX(DD, BB) \
+  if (head_size == DD && block_size == BB) return launch_prefix<T, DD, BB>(p, num_seqs, max_query_len, device, stream);
+#ifdef B200_FAST_BUILD
+  B200_PFX(64, 16) B200_PFX(128, 16)
+#else
+#define B200_PFX_D(DD) B200_PFX(DD, 8) B200_PFX(DD, 16) B200_PFX(DD, 32)
+  B200_PFX_D(64) B200_PFX_D(80) B200_PFX_D(96) B200_PFX_D(112) B200_PFX_D(120) B200_PFX_D(128)
+  B200_PFX_D(192) B200_PFX_D(256)
+#undef B200_PFX_D
+#endif
+#undef B200_PFX
+  if (block_size != 8 && block_size != 16 && block_size != 32)
+    set_error("Unsupported block size: %d", block_size);
+  else
+    set_error("Unsupported head size: %d", head_size);
+  return B200_ERR_UNSUPPORTED;
+}
+
+}  // namespace
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_context_attention_fwd(
+    const void* q, const void* k, const void* v, void* out, const void* key_cache,
+    const void* value_cache, const int32_t* block_tables, const int32_t* start_loc,
+    const int32_t* seq_lens, const int32_t* ctx_lens, int num_seqs, int num_heads, int num_kv_heads,
+    int head_size, int block_size, int max_blocks_per_seq, int max_query_len, int64_t q_stride0,
+    int64_t q_stride1, int64_t k_stride0, int64_t k_stride1, int64_t v_stride0, int64_t v_stride1,
+    int64_t o_stride0, int64_t o_stride1, int64_t kc_block_stride, int64_t kc_head_stride,
+    int64_t vc_block_stride, int64_t vc_head_stride, const float* alibi_slopes, int sliding_window,
+    float scale, int dtype, int device, b200_stream_t stream) {
+  B200_CHECK_ARG(num_seqs >= 0 && max_query_len >= 0 && head_size > 0 && block_size > 0,
+                 "context_attention_fwd: bad sizes");
+  if (num_seqs == 0 || max_query_len == 0) return B200_OK;
+  B200_CHECK_ARG(num_kv_heads > 0 && num_heads % num_kv_heads == 0,
+                 "num_heads (%d) must be a positive multiple of num_kv_heads (%d)", num_heads, num_kv_heads);
+  if (dtype != B200_DT_F16 && dtype != B200_DT_BF16) {
+    set_error("Unsupported data type: context_attention_fwd runs fp16 / bf16 (got %d)", dtype);
+    return B200_ERR_UNSUPPORTED;
+  }
+  auto a16 = [](const void* ptr) { return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0; };
+  B200_CHECK_ARG(a16(k) && a16(v) && a16(key_cache) && a16(value_cache) && k_stride0 % 8 == 0 &&
+                     k_stride1 % 8 == 0 && v_stride0 % 8 == 0 && v_stride1 % 8 == 0 &&
+                     kc_block_stride % 8 == 0 && kc_head_stride % 8 == 0 && vc_block_stride % 8 == 0 &&
+                     vc_head_stride % 8 == 0,
+                 "context_attention_fwd: k/v/cache rows must be 16-byte aligned");
+  B200_CHECK_ARG((reinterpret_cast<uintptr_t>(q) & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 3) == 0 &&
+                     q_stride0 % 2 == 0 && q_stride1 % 2 == 0 && o_stride0 % 2 == 0 && o_stride1 % 2 == 0,
+                 "context_attention_fwd: q/out rows must be 4-byte aligned");
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  int dev = device;
+  if (dev < 0) B200_CUDA_OK(cudaGetDevice(&dev));
+  PrefixParams p{};
+  p.q = q; p.k = k; p.v = v; p.out = out; p.k_cache = key_cache; p.v_cache = value_cache;
+  p.block_tables = block_tables; p.start_loc = start_loc; p.seq_lens = seq_lens; p.ctx_lens = ctx_lens;
+  p.alibi_slopes = alibi_slopes;
+  p.num_heads = num_heads; p.num_kv_heads = num_kv_heads; p.group = num_heads / num_kv_heads;
+  p.max_blocks_per_seq = max_blocks_per_seq;
+  p.sliding_window = (sliding_window > 0 && alibi_slopes == nullptr) ? sliding_window : 0;  // :713-811
+  p.q_s0 = q_stride0; p.q_s1 = q_stride1; p.k_s0 = k_stride0; p.k_s1 = k_stride1;
+  p.v_s0 = v_stride0; p.v_s1 = v_stride1; p.o_s0 = o_stride0; p.o_s1 = o_stride1;
+  p.kc_bs = kc_block_stride; p.kc_hs = kc_head_stride; p.vc_bs = vc_block_stride; p.vc_hs = vc_head_stride;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  if (dtype == B200_DT_F16)
+    return dispatch_prefix<__half>(p, head_size, block_size, num_seqs, max_query_len, dev, (cudaStream_t)stream);
+  return dispatch_prefix<__nv_bfloat16>(p, head_size, block_size, num_seqs, max_query_len, dev, (cudaStream_t)stream);
+}

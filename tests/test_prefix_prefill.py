@@ -78,3 +78,115 @@ def test_oracle_edge_cases(oracle):
     c = make_prefix_case([0, 15, 16, 40], [7, 1, 1, 0], 6, 2, 64, 16, torch.bfloat16, seed=5, q_pad=8)
     o = _call(oracle.context_attention_fwd, c, torch.zeros_like(c["query"]))
     assert (o.double() - ground_truth(c)).abs().max().item() <= 1e-2
+
+
+# ---------------------------------------------------------------- product path (GPU) ----
+def _gpu(c, slopes=None, window=0):
+    from light_vllm_b200.attention.prefix_prefill import context_attention_fwd
+    d = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in c.items()}
+    out = torch.full_like(d["query"], float("nan"))
+    _call(context_attention_fwd, d, out, slopes.cuda() if slopes is not None else None, window)
+    torch.cuda.synchronize()
+    return out.cpu()
+
+
+@pytest.mark.gpu
+def test_kernel_matches_reference_golden():
+    """fp16 golden cases directly; fp32 golden cases are re-run in fp16 against the oracle."""
+    n = 0
+    for g in torch.load(GOLD):
+        if g["dtype"] != torch.float16:
+            continue
+        c = make_prefix_case(g["ctx_lens"], g["query_lens"], g["H"], g["KH"], g["D"], g["BS"],
+                             g["dtype"], g["seed"])
+        o = _gpu(c, g["alibi_slopes"], g["sliding_window"])
+        err = (o.float() - g["out"].float()).abs().max().item()
+        assert err <= 2e-3, (g["D"], g["BS"], err)
+        n += 1
+    assert n >= 3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("H,KH,D,BS", [(32, 8, 128, 16), (28, 4, 128, 16), (14, 2, 64, 16),
+                                       (8, 8, 64, 32), (4, 4, 256, 16), (6, 2, 120, 8),
+                                       (16, 1, 96, 16), (4, 2, 192, 32)])
+def test_kernel_matches_oracle(oracle, dtype, H, KH, D, BS):
+    ctx = [0, 5, 16, 129, 700, 48]
+    ql = [70, 1, 33, 64, 130, 0]
+    c = make_prefix_case(ctx, ql, H, KH, D, BS, dtype, seed=H + D, q_pad=8)
+    want = _call(oracle.context_attention_fwd, c, torch.zeros_like(c["query"]))
+    got = _gpu(c)
+    assert torch.isfinite(got.float()).all()
+    assert (got.float() - want.float()).abs().max().item() <= TOL[dtype]
+    assert (got.double() - ground_truth(c)).abs().max().item() <= TOL[dtype]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("window", [1, 7, 16, 100, 4096])
+def test_kernel_sliding_window(oracle, window):
+    c = make_prefix_case([300, 20, 0], [90, 40, 50], 8, 2, 128, 16, torch.float16, seed=window)
+    want = _call(oracle.context_attention_fwd, c, torch.zeros_like(c["query"]), None, window)
+    got = _gpu(c, None, window)
+    assert (got.float() - want.float()).abs().max().item() <= 2e-3
+    assert (got.double() - ground_truth(c, None, window)).abs().max().item() <= 2e-3
+
+
+@pytest.mark.gpu
+def test_kernel_alibi(oracle):
+    H = 8
+    slopes = torch.tensor([2.0 ** (-(j + 1) * 8.0 / H) for j in range(H)], dtype=torch.float32)
+    c = make_prefix_case([200, 0, 33], [60, 100, 17], H, 2, 128, 16, torch.bfloat16, seed=9)
+    want = _call(oracle.context_attention_fwd, c, torch.zeros_like(c["query"]), slopes)
+    got = _gpu(c, slopes)
+    assert (got.float() - want.float()).abs().max().item() <= 1e-2
+    assert (got.double() - ground_truth(c, slopes)).abs().max().item() <= 1e-2
+
+
+@pytest.mark.gpu
+def test_kernel_poisoned_cache_tail_and_spare_rows():
+    """Cache slots past ctx_len (where the new tokens will be written) may hold anything."""
+    c = make_prefix_case([21, 40], [30, 9], 8, 2, 128, 16, torch.float16, seed=2)
+    BS = 16
+    for b, ctx in enumerate([21, 40]):
+        if ctx % BS:
+            blk = int(c["block_tables"][b, ctx // BS])
+            c["key_cache"][blk, :, :, ctx % BS:, :] = float("nan")
+            c["value_cache"][blk, :, :, ctx % BS:] = float("nan")
+    got = _gpu(c)
+    assert torch.isfinite(got.float()).all()
+    assert (got.double() - ground_truth(c)).abs().max().item() <= 2e-3
+
+
+@pytest.mark.gpu
+def test_plugin_prefix_prefill_then_decode(oracle):
+    """PagedB200AttentionImpl.forward with a prefix-cache hit: the new tokens are written to the cache
+    and attend the cached prefix (forward_prefix); a following decode step sees all of them."""
+    from light_vllm_b200.attention.backend import PagedB200AttentionImpl, PagedB200AttentionMetadata
+    H, KH, D, BS = 8, 2, 128, 16
+    ctx, ql = [32, 5], [20, 11]
+    c = make_prefix_case(ctx, ql, H, KH, D, BS, torch.float16, seed=12)
+    dev = "cuda:0"
+    NB = c["key_cache"].shape[0]
+    kv_cache = torch.stack([c["key_cache"].reshape(NB, -1), c["value_cache"].reshape(NB, -1)]).to(dev)
+    T = sum(ql)
+    slots = []
+    for b in range(2):
+        for i in range(ql[b]):
+            pos = ctx[b] + i
+            slots.append(int(c["block_tables"][b, pos // BS]) * BS + pos % BS)
+    meta = PagedB200AttentionMetadata(
+        num_prefills=2, num_prefill_tokens=T, num_decode_tokens=0,
+        slot_mapping=torch.tensor(slots, dtype=torch.int64, device=dev),
+        seq_lens=[a + b for a, b in zip(ctx, ql)], seq_lens_tensor=c["seq_lens"].to(dev),
+        max_query_len=max(ql), max_prefill_seq_len=max(a + b for a, b in zip(ctx, ql)),
+        max_decode_seq_len=0, query_start_loc=c["query_start_loc"].to(dev),
+        seq_start_loc=torch.tensor([0, ctx[0] + ql[0], sum(ctx) + sum(ql)], dtype=torch.int32, device=dev),
+        context_lens_tensor=c["context_lens"].to(dev),
+        block_tables=c["block_tables"].to(dev), use_cuda_graph=False)
+    impl = PagedB200AttentionImpl(H, D, D ** -0.5, KH, None, None, "auto")
+    q = c["query"].reshape(T, H * D).to(dev)
+    k = c["key"].reshape(T, KH * D).to(dev)
+    v = c["value"].reshape(T, KH * D).to(dev)
+    out = impl.forward(q, k, v, kv_cache, meta).view(T, H, D).cpu()
+    assert (out.double() - ground_truth(c)).abs().max().item() <= 2e-3
