@@ -114,9 +114,9 @@ __device__ __forceinline__ void fp8x4_to_f16x2x2(uint32_t w, uint32_t& lo, uint3
 //   then needs V[d][4*qq..4*qq+3] = one 32-bit shared load per d-tile instead of two 16-bit ones,
 //   and both K-row sets {0,1,4,5,10,11,14,15} / {2,3,6,7,8,9,12,13} still cover all 8 16-byte
 //   bank groups, so the K loads stay conflict-free.
-template <int KV, int BS>
+template <int KV, int BS, bool PERM16 = false>
 __device__ __forceinline__ int page_token(int nt, int qq, int e) {
-  if constexpr (KV != B200_KV_AUTO && BS >= 16)
+  if constexpr ((KV != B200_KV_AUTO || PERM16) && BS >= 16)
     return (nt >> 1) * 16 + 4 * qq + 2 * ((nt & 1) ^ (qq >> 1)) + e;
   else
     return nt * 8 + 2 * qq + e;
@@ -127,7 +127,12 @@ __device__ __forceinline__ int page_token(int nt, int qq, int e) {
 // ROWB (prefix prefill): every row has its own window of visible tokens [row_lo, row_hi) inside the
 // page (causal frontier / sliding window) and its own ALiBi origin row_rel0 = (first token of the
 // page) - (the row's query position); decode rows all share `valid` and `tok_rel0`.
-template <typename T, int D, int BS, int KV, int GROWS, bool TAIL, bool PLAIN, bool ROWB>
+// PFX (prefill kernel, 16-bit caches, >= 16-token pages): the compute-bound variant.  Tokens take the
+// permuted order of page_token<.., true> so that P.V reads V[d][4*q4..4*q4+3] with ONE conflict-free
+// 64-bit shared load per d-tile (ldmatrix over the 32-byte V rows is 2-way bank conflicted), and
+// Q.K^T accumulates even / odd k-steps in separate chains (half the dependent-HMMA latency).
+template <typename T, int D, int BS, int KV, int GROWS, bool TAIL, bool PLAIN, bool ROWB,
+          bool PFX = false>
 __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem,
                                                 const uint32_t (&qa)[(D + 15) / 16][GROWS / 4],
                                                 float (&o)[D / 8][GROWS / 4], float (&m)[GROWS / 8],
@@ -155,7 +160,13 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
   if constexpr (KV == B200_KV_AUTO) {
     // K page layout [D/8][BS][8] (16-byte rows).  ldmatrix row addresses for this lane.
     if constexpr (BS >= 16) {
-      const uint32_t base = k_smem + (uint32_t)((mi & 1) * BS * 16 + ((mi >> 1) * 8 + r8) * 16);
+      const int krow = PFX ? page_token<KV, BS, true>(mi >> 1, r8 >> 1, r8 & 1) : (mi >> 1) * 8 + r8;
+      const uint32_t base = k_smem + (uint32_t)((mi & 1) * BS * 16 + krow * 16);
+      float s2[PFX ? NT : 1][4];
+      if constexpr (PFX) {
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) s2[nt][0] = s2[nt][1] = s2[nt][2] = s2[nt][3] = 0.f;
+      }
 #pragma unroll
       for (int ks = 0; ks < KS; ++ks) {
 #pragma unroll
@@ -164,9 +175,20 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
           ldsm_x4(base + (uint32_t)(ks * 2 * BS * 16 + th * 16 * 16), b00, b01, b10, b11);
           if (2 * ks + 1 >= NDT) b01 = b11 = 0u;  // odd chunk count (head 120): no such chunk
           const uint32_t a1 = (RS == 2) ? qa[ks][2] : 0u, a3 = (RS == 2) ? qa[ks][3] : 0u;
-          MmaOp<MT>::run(s[2 * th], qa[ks][0], a1, qa[ks][1], a3, b00, b01);
-          MmaOp<MT>::run(s[2 * th + 1], qa[ks][0], a1, qa[ks][1], a3, b10, b11);
+          if (PFX && (ks & 1)) {
+            MmaOp<MT>::run(s2[PFX ? 2 * th : 0], qa[ks][0], a1, qa[ks][1], a3, b00, b01);
+            MmaOp<MT>::run(s2[PFX ? 2 * th + 1 : 0], qa[ks][0], a1, qa[ks][1], a3, b10, b11);
+          } else {
+            MmaOp<MT>::run(s[2 * th], qa[ks][0], a1, qa[ks][1], a3, b00, b01);
+            MmaOp<MT>::run(s[2 * th + 1], qa[ks][0], a1, qa[ks][1], a3, b10, b11);
+          }
         }
+      }
+      if constexpr (PFX) {
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) s[nt][e] += s2[nt][e];
       }
     } else {  // BS == 8: one n-tile, ldmatrix.x2 (lanes 0-15 supply addresses)
       const uint32_t base = k_smem + (uint32_t)((mi & 1) * BS * 16 + r8 * 16);
@@ -211,7 +233,7 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
     for (int nt = 0; nt < NT; ++nt) {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        const int t = page_token<KV, BS>(nt, q4, e);  // token within page
+        const int t = page_token<KV, BS, PFX>(nt, q4, e);  // token within page
         float x = s[nt][2 * rs + e] * scale_log2;
         if constexpr (!PLAIN) x += slope[rs] * ((ROWB ? row_rel0[rs] : tok_rel0) + (float)t);
         if (TAIL && t >= valid) x = kNegInf;
@@ -260,7 +282,7 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
   if constexpr (TAIL) {
 #pragma unroll
     for (int h = 0; h < (BS >= 16 ? BS / 8 : 1); ++h) {
-      const int t0 = page_token<KV, BS>(h, q4, 0);
+      const int t0 = page_token<KV, BS, PFX>(h, q4, 0);
       vmask[h] = (t0 < valid ? 0x0000ffffu : 0u) | (t0 + 1 < valid ? 0xffff0000u : 0u);
     }
   }
@@ -278,7 +300,26 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
       pa1 = (RS == 2) ? MmaOp<MT>::pack(s[0][2], s[0][3]) : 0u;
       pa2 = pa3 = 0u;
     }
-    if constexpr (KV == B200_KV_AUTO) {
+    if constexpr (KV == B200_KV_AUTO && PFX && BS >= 16) {
+      // V page [D][BS] 16-bit: this lane's P fragments cover tokens 4*q4..4*q4+3 of the 16-token
+      // group (page_token<.., true>): one 64-bit load per d-tile, a warp reads 256 contiguous bytes.
+      const uint32_t base = v_smem + (uint32_t)((lane >> 2) * BS * 2 + q4 * 8 + kk * 32);
+#pragma unroll
+      for (int j = 0; j < NDT; ++j) {
+        uint32_t w0, w1;
+        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(base + (uint32_t)(j * 8 * BS * 2)));
+        uint32_t b0 = (q4 & 2) ? w1 : w0, b1 = (q4 & 2) ? w0 : w1;
+        if constexpr (TAIL) {
+          b0 &= vmask[2 * kk];
+          b1 &= vmask[2 * kk + 1];
+        }
+        float acc[4] = {o[j][0], o[j][1], RS == 2 ? o[j][2 * (RS - 1)] : 0.f,
+                        RS == 2 ? o[j][2 * (RS - 1) + 1] : 0.f};
+        MmaOp<MT>::run(acc, pa0, pa1, pa2, pa3, b0, b1);
+        o[j][0] = acc[0]; o[j][1] = acc[1];
+        if constexpr (RS == 2) { o[j][2] = acc[2]; o[j][3] = acc[3]; }
+      }
+    } else if constexpr (KV == B200_KV_AUTO) {
       if constexpr (BS >= 16) {
         // V page [D][BS]: 8x8 matrices = 8 d-rows x 8 tokens (16 B); x4 = 2 d-tiles x 2 token halves
         const uint32_t base = v_smem + (uint32_t)((((mi >> 1) * 8 + r8) * BS * 2) + (mi & 1) * 16 +

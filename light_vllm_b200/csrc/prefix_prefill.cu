@@ -33,7 +33,7 @@ struct PrefixParams {
 constexpr int kPrefixWarps = 4;
 
 template <typename T, int D, int BS, int GROWS, bool PLAIN>
-__global__ void __launch_bounds__(kPrefixWarps * 32)
+__global__ void __launch_bounds__(kPrefixWarps * 32, (D <= 128 ? 3 : 1))
 context_attention_kernel(const __grid_constant__ PrefixParams p) {
   constexpr int KV = B200_KV_AUTO;
   constexpr int PAGE_BYTES = D * BS * 2;
@@ -140,7 +140,8 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
         static_cast<const unsigned char*>(p.k_cache) + (int64_t)kvh * p.kc_hs * 2;
     const unsigned char* vbase =
         static_cast<const unsigned char*>(p.v_cache) + (int64_t)kvh * p.vc_hs * 2;
-    const uint64_t policy = l2_policy_evict_first();
+    // every query tile of this (sequence, kv head) re-reads the same pages: keep them in L2
+    const uint64_t policy = l2_policy_evict_last();
     int win0 = 0;
     int tbl = (warp == 0 && lane < n) ? bt[lane] : 0;
     auto issue = [&](int i) {  // warp 0, all lanes: page i -> stage i % NS
@@ -184,15 +185,15 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
         const bool tail = tok0 + BS > ctx;
         const bool windowed = W > 0 && (ctx + w_tok_hi - W + 1 > tok0);
         if (tail)
-          process_page_ex<T, D, BS, KV, GROWS, true, PLAIN, true>(
+          process_page_ex<T, D, BS, KV, GROWS, true, PLAIN, true, true>(
               ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, ctx - tok0, p.scale_log2, slope, 0.f, row_on,
               row_lo, row_hi, row_rel0);
         else if (windowed || !PLAIN)
-          process_page_ex<T, D, BS, KV, GROWS, false, PLAIN, true>(
+          process_page_ex<T, D, BS, KV, GROWS, false, PLAIN, true, true>(
               ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS, p.scale_log2, slope, 0.f, row_on, row_lo,
               row_hi, row_rel0);
         else
-          process_page_ex<T, D, BS, KV, GROWS, false, true, false>(
+          process_page_ex<T, D, BS, KV, GROWS, false, true, false, true>(
               ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS, p.scale_log2, slope, 0.f, row_on, row_lo,
               row_hi, row_rel0);
       }
@@ -263,11 +264,11 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
         const bool frontier = t0 + BS - 1 > w_tok_lo;
         const bool windowed = W > 0 && (w_tok_hi - W + 1 > t0);
         if (frontier || windowed || !PLAIN)
-          process_page_ex<T, D, BS, KV, GROWS, false, PLAIN, true>(
+          process_page_ex<T, D, BS, KV, GROWS, false, PLAIN, true, true>(
               ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS, p.scale_log2, slope, 0.f, row_on, row_lo,
               row_hi, row_rel0);
         else
-          process_page_ex<T, D, BS, KV, GROWS, false, true, false>(
+          process_page_ex<T, D, BS, KV, GROWS, false, true, false, true>(
               ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS, p.scale_log2, slope, 0.f, row_on, row_lo,
               row_hi, row_rel0);
       }
@@ -308,8 +309,8 @@ int launch_prefix(PrefixParams& p, int num_seqs, int max_query_len, int device, 
   B200_CHECK_ARG(p.group <= ROWS, "context_attention_fwd: %d q-heads per kv-head exceed the %d-row tile",
                  p.group, ROWS);
   p.tok_tile = ROWS / p.group;
-  int ns = 4;
-  while (ns > 2 && prefix_smem<D, BS>(ns) > (size_t)100 * 1024) --ns;
+  int ns = 8;  // ring depth: three CTAs per SM must still fit in 227 KiB
+  while (ns > 2 && prefix_smem<D, BS>(ns) > (size_t)72 * 1024) --ns;
   p.num_stages = ns;
   const size_t smem = prefix_smem<D, BS>(ns);
   const bool plain = p.alibi_slopes == nullptr;
