@@ -142,16 +142,17 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
         static_cast<const unsigned char*>(p.v_cache) + (int64_t)kvh * p.vc_hs * 2;
     // every query tile of this (sequence, kv head) re-reads the same pages: keep them in L2
     const uint64_t policy = l2_policy_evict_last();
+    // The producer role rotates over the warps (page j is issued by warp j % 4), so no warp carries
+    // the whole issue overhead; every warp keeps its own 32-entry block-table window.
     int win0 = 0;
-    int tbl = (warp == 0 && lane < n) ? bt[lane] : 0;
-    auto issue = [&](int i) {  // warp 0, all lanes: page i -> stage i % NS
-      if (i >= win0 + 32) {
+    int tbl = (lane < n) ? bt[lane] : 0;
+    auto issue = [&](int i, int s) {  // one warp, all lanes: page i -> stage s
+      while (i >= win0 + 32) {
         win0 += 32;
         tbl = (win0 + lane < n) ? bt[win0 + lane] : 0;
       }
       const int64_t blk = __shfl_sync(0xffffffffu, tbl, i - win0);
       if (elect_one()) {
-        const int s = i % NS;
         const uint32_t bar = full_u32 + 8 * s;
         const uint32_t dst = ring_u32 + (uint32_t)s * STAGE_BYTES;
         mbar_arrive_expect_tx(bar, STAGE_BYTES);
@@ -161,15 +162,17 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
     };
     if (warp == 0) {
       const int pre = min(NS, n);
-      for (int i = 0; i < pre; ++i) issue(i);
+      for (int i = 0; i < pre; ++i) issue(i, i);
     }
+    int s = 0, sp = 0;          // stage of page i / of page i - 1
+    uint32_t par = 0, pp = 0;   // their mbarrier phase parities
     for (int i = 0; i < n; ++i) {
-      const int s = i % NS;
-      if (warp == 0 && i >= 1 && i - 1 + NS < n) {  // refill the stage every warp left one page ago
-        mbar_wait(empty_u32 + 8 * ((i - 1) % NS), (uint32_t)(((i - 1) / NS) & 1));
-        issue(i - 1 + NS);
+      if (i >= 1 && i - 1 + NS < n && warp == ((i - 1) & (kPrefixWarps - 1))) {
+        // refill the stage every warp left one page ago
+        mbar_wait(empty_u32 + 8 * sp, pp);
+        issue(i - 1 + NS, sp);
       }
-      mbar_wait(full_u32 + 8 * s, (uint32_t)((i / NS) & 1));
+      mbar_wait(full_u32 + 8 * s, par);
       if (warp_on) {
         const int tok0 = (page0 + i) * BS;
         const uint32_t ksm = ring_u32 + (uint32_t)s * STAGE_BYTES;
@@ -199,6 +202,12 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(empty_u32 + 8 * s);
+      sp = s;
+      pp = par;
+      if (++s == NS) {
+        s = 0;
+        par ^= 1u;
+      }
     }
   }
   __syncthreads();  // the ring becomes the staging area of phase 2
