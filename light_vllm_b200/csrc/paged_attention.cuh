@@ -131,8 +131,10 @@ __device__ __forceinline__ int page_token(int nt, int qq, int e) {
 // permuted order of page_token<.., true> so that P.V reads V[d][4*q4..4*q4+3] with ONE conflict-free
 // 64-bit shared load per d-tile (ldmatrix over the 32-byte V rows is 2-way bank conflicted), and
 // Q.K^T accumulates even / odd k-steps in separate chains (half the dependent-HMMA latency).
+// PGS (PFX only): pages consumed per step.  PGS = 2 treats two 16-token pages, `pg_stride` bytes
+// apart in shared memory, as one 32-token step: twice the independent HMMA work per softmax round.
 template <typename T, int D, int BS, int KV, int GROWS, bool TAIL, bool PLAIN, bool ROWB,
-          bool PFX = false>
+          bool PFX = false, int PGS = 1>
 __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem,
                                                 const uint32_t (&qa)[(D + 15) / 16][GROWS / 4],
                                                 float (&o)[D / 8][GROWS / 4], float (&m)[GROWS / 8],
@@ -142,11 +144,15 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
                                                 const bool (&row_on)[GROWS / 8],
                                                 const int (&row_lo)[GROWS / 8],
                                                 const int (&row_hi)[GROWS / 8],
-                                                const float (&row_rel0)[GROWS / 8]) {
+                                                const float (&row_rel0)[GROWS / 8],
+                                                uint32_t pg_stride = 0) {
   using MT = typename MmaType<T, KV>::type;
+  static_assert(PGS == 1 || (PFX && KV == B200_KV_AUTO && BS >= 16), "multi-page steps: PFX only");
   constexpr int ES = KvTraits<KV>::ES;
   constexpr int KS = (D + 15) / 16;  // k-steps over head dim
-  constexpr int NT = BS / 8;         // 8-token n-tiles in a page
+  constexpr int TB = BS * PGS;       // tokens per step
+  constexpr int GPP = BS >= 16 ? BS / 16 : 1;  // 16-token groups per page
+  constexpr int NT = TB / 8;         // 8-token n-tiles in a step
   constexpr int RS = GROWS / 8;      // row sets (rows g, g+8)
   constexpr int NDT = D / 8;         // 8-wide d tiles of the output
   const int q4 = lane & 3;
@@ -162,8 +168,9 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
     if constexpr (BS >= 16) {
       const int krow = PFX ? page_token<KV, BS, true>(mi >> 1, r8 >> 1, r8 & 1) : (mi >> 1) * 8 + r8;
       const uint32_t base = k_smem + (uint32_t)((mi & 1) * BS * 16 + krow * 16);
-      float s2[PFX ? NT : 1][4];
-      if constexpr (PFX) {
+      constexpr bool SPLIT = PFX && PGS == 1;  // two accumulation chains per n-tile
+      float s2[SPLIT ? NT : 1][4];
+      if constexpr (SPLIT) {
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) s2[nt][0] = s2[nt][1] = s2[nt][2] = s2[nt][3] = 0.f;
       }
@@ -172,19 +179,20 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
 #pragma unroll
         for (int th = 0; th < NT / 2; ++th) {  // 16 tokens per ldmatrix.x4
           uint32_t b00, b01, b10, b11;
-          ldsm_x4(base + (uint32_t)(ks * 2 * BS * 16 + th * 16 * 16), b00, b01, b10, b11);
+          ldsm_x4(base + (uint32_t)(ks * 2 * BS * 16 + (th % GPP) * 16 * 16) + (th / GPP) * pg_stride,
+                  b00, b01, b10, b11);
           if (2 * ks + 1 >= NDT) b01 = b11 = 0u;  // odd chunk count (head 120): no such chunk
           const uint32_t a1 = (RS == 2) ? qa[ks][2] : 0u, a3 = (RS == 2) ? qa[ks][3] : 0u;
-          if (PFX && (ks & 1)) {
-            MmaOp<MT>::run(s2[PFX ? 2 * th : 0], qa[ks][0], a1, qa[ks][1], a3, b00, b01);
-            MmaOp<MT>::run(s2[PFX ? 2 * th + 1 : 0], qa[ks][0], a1, qa[ks][1], a3, b10, b11);
+          if (SPLIT && (ks & 1)) {
+            MmaOp<MT>::run(s2[SPLIT ? 2 * th : 0], qa[ks][0], a1, qa[ks][1], a3, b00, b01);
+            MmaOp<MT>::run(s2[SPLIT ? 2 * th + 1 : 0], qa[ks][0], a1, qa[ks][1], a3, b10, b11);
           } else {
             MmaOp<MT>::run(s[2 * th], qa[ks][0], a1, qa[ks][1], a3, b00, b01);
             MmaOp<MT>::run(s[2 * th + 1], qa[ks][0], a1, qa[ks][1], a3, b10, b11);
           }
         }
       }
-      if constexpr (PFX) {
+      if constexpr (SPLIT) {
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
@@ -233,7 +241,7 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
     for (int nt = 0; nt < NT; ++nt) {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        const int t = page_token<KV, BS, PFX>(nt, q4, e);  // token within page
+        const int t = page_token<KV, TB, PFX>(nt, q4, e);  // token within the step
         float x = s[nt][2 * rs + e] * scale_log2;
         if constexpr (!PLAIN) x += slope[rs] * ((ROWB ? row_rel0[rs] : tok_rel0) + (float)t);
         if (TAIL && t >= valid) x = kNegInf;
@@ -278,15 +286,15 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
 
   // ---------------- O += P V ----------------
   // tail masks: V columns past the sequence end may hold NaN; 0 * NaN must not reach the MMA.
-  uint32_t vmask[BS >= 16 ? BS / 8 : 1];
+  uint32_t vmask[TB >= 16 ? TB / 8 : 1];
   if constexpr (TAIL) {
 #pragma unroll
-    for (int h = 0; h < (BS >= 16 ? BS / 8 : 1); ++h) {
-      const int t0 = page_token<KV, BS, PFX>(h, q4, 0);
+    for (int h = 0; h < (TB >= 16 ? TB / 8 : 1); ++h) {
+      const int t0 = page_token<KV, TB, PFX>(h, q4, 0);
       vmask[h] = (t0 < valid ? 0x0000ffffu : 0u) | (t0 + 1 < valid ? 0xffff0000u : 0u);
     }
   }
-  constexpr int KSV = (BS >= 16) ? BS / 16 : 1;  // k-steps over tokens
+  constexpr int KSV = (TB >= 16) ? TB / 16 : 1;  // k-steps over tokens
 #pragma unroll
   for (int kk = 0; kk < KSV; ++kk) {
     uint32_t pa0, pa1, pa2, pa3;
@@ -303,7 +311,8 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
     if constexpr (KV == B200_KV_AUTO && PFX && BS >= 16) {
       // V page [D][BS] 16-bit: this lane's P fragments cover tokens 4*q4..4*q4+3 of the 16-token
       // group (page_token<.., true>): one 64-bit load per d-tile, a warp reads 256 contiguous bytes.
-      const uint32_t base = v_smem + (uint32_t)((lane >> 2) * BS * 2 + q4 * 8 + kk * 32);
+      const uint32_t base = v_smem + (uint32_t)((lane >> 2) * BS * 2 + q4 * 8 + (kk % GPP) * 32) +
+                            (kk / GPP) * pg_stride;
 #pragma unroll
       for (int j = 0; j < NDT; ++j) {
         uint32_t w0, w1;

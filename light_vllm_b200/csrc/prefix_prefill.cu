@@ -25,7 +25,8 @@ struct PrefixParams {
   const void *k_cache, *v_cache;
   const int32_t *block_tables, *start_loc, *seq_lens, *ctx_lens;
   const float* alibi_slopes;
-  int num_heads, num_kv_heads, group, max_blocks_per_seq, sliding_window, tok_tile, num_stages;
+  int num_heads, num_kv_heads, group, max_blocks_per_seq, sliding_window, tok_tile, num_stages,
+      stage_shift;
   int64_t q_s0, q_s1, k_s0, k_s1, v_s0, v_s1, o_s0, o_s1, kc_bs, kc_hs, vc_bs, vc_hs;
   float scale_log2;
 };
@@ -164,17 +165,26 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
       const int pre = min(NS, n);
       for (int i = 0; i < pre; ++i) issue(i, i);
     }
-    int s = 0, sp = 0;          // stage of page i / of page i - 1
-    uint32_t par = 0, pp = 0;   // their mbarrier phase parities
-    for (int i = 0; i < n; ++i) {
-      if (i >= 1 && i - 1 + NS < n && warp == ((i - 1) & (kPrefixWarps - 1))) {
-        // refill the stage every warp left one page ago
-        mbar_wait(empty_u32 + 8 * sp, pp);
-        issue(i - 1 + NS, sp);
+    // NS is a power of two: stage of page j = j & (NS - 1), phase parity = (j >> stage_shift) & 1.
+    const int smask = NS - 1, sshift = p.stage_shift;
+    constexpr bool kPairOk = PLAIN && BS == 16;  // two pages per step on the unmasked fast path
+    int i = 0, i_prev = 0, next_issue = min(NS, n);
+    while (i < n) {
+      // refill the stages every warp left at least one step ago (pages below i_prev)
+      while (next_issue < n && next_issue - NS < i_prev) {
+        const int j = next_issue++;
+        if (warp == (j & (kPrefixWarps - 1))) {
+          mbar_wait(empty_u32 + 8 * (j & smask), (uint32_t)(((j >> sshift) - 1) & 1));
+          issue(j, j & smask);
+        }
       }
-      mbar_wait(full_u32 + 8 * s, par);
+      const int s = i & smask;
+      const int tok0 = (page0 + i) * BS;
+      const bool pair = kPairOk && W == 0 && i + 1 < n && tok0 + 2 * BS <= ctx;
+      const int s1 = (i + 1) & smask;
+      mbar_wait(full_u32 + 8 * s, (uint32_t)((i >> sshift) & 1));
+      if (pair) mbar_wait(full_u32 + 8 * s1, (uint32_t)(((i + 1) >> sshift) & 1));
       if (warp_on) {
-        const int tok0 = (page0 + i) * BS;
         const uint32_t ksm = ring_u32 + (uint32_t)s * STAGE_BYTES;
         int row_lo[RS], row_hi[RS];
         float row_rel0[RS];
@@ -187,7 +197,16 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
         }
         const bool tail = tok0 + BS > ctx;
         const bool windowed = W > 0 && (ctx + w_tok_hi - W + 1 > tok0);
-        if (tail)
+        if constexpr (kPairOk) {
+          if (pair) {
+            const uint32_t stride = (uint32_t)(s1 - s) * (uint32_t)STAGE_BYTES;  // wraps for s1 < s
+            process_page_ex<T, D, BS, KV, GROWS, false, true, false, true, 2>(
+                ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, 2 * BS, p.scale_log2, slope, 0.f, row_on,
+                row_lo, row_hi, row_rel0, stride);
+          }
+        }
+        if (pair) {
+        } else if (tail)
           process_page_ex<T, D, BS, KV, GROWS, true, PLAIN, true, true>(
               ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, ctx - tok0, p.scale_log2, slope, 0.f, row_on,
               row_lo, row_hi, row_rel0);
@@ -201,13 +220,12 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
               row_hi, row_rel0);
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(empty_u32 + 8 * s);
-      sp = s;
-      pp = par;
-      if (++s == NS) {
-        s = 0;
-        par ^= 1u;
+      if (lane == 0) {
+        mbar_arrive(empty_u32 + 8 * s);
+        if (pair) mbar_arrive(empty_u32 + 8 * s1);
       }
+      i_prev = i;
+      i += pair ? 2 : 1;
     }
   }
   __syncthreads();  // the ring becomes the staging area of phase 2
@@ -318,9 +336,10 @@ int launch_prefix(PrefixParams& p, int num_seqs, int max_query_len, int device, 
   B200_CHECK_ARG(p.group <= ROWS, "context_attention_fwd: %d q-heads per kv-head exceed the %d-row tile",
                  p.group, ROWS);
   p.tok_tile = ROWS / p.group;
-  int ns = 8;  // ring depth: three CTAs per SM must still fit in 227 KiB
-  while (ns > 2 && prefix_smem<D, BS>(ns) > (size_t)72 * 1024) --ns;
+  int ns = 8;  // ring depth (a power of two): three CTAs per SM must still fit in 227 KiB
+  while (ns > 2 && prefix_smem<D, BS>(ns) > (size_t)72 * 1024) ns /= 2;
   p.num_stages = ns;
+  p.stage_shift = ns == 8 ? 3 : ns == 4 ? 2 : 1;
   const size_t smem = prefix_smem<D, BS>(ns);
   const bool plain = p.alibi_slopes == nullptr;
   auto kern = plain ? context_attention_kernel<T, D, BS, GROWS, true>
