@@ -84,7 +84,8 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
     const size_t row_off = slot_off + ((size_t)rank * max_pairs + pair) * row_floats;
     for (int d0 = 2 * lane; d0 < head_size; d0 += 64) {
       float a0 = 0.f, a1 = 0.f;
-      for (int j = 0; j < np; ++j) {
+#pragma unroll 8
+      for (int j = 0; j < np; ++j) {  // independent loads: unrolled so that they overlap
         const float wj = w[j] * inv;
         a0 += to_f32<T>(t[(int64_t)j * head_size + d0]) * wj;
         a1 += to_f32<T>(t[(int64_t)j * head_size + d0 + 1]) * wj;
