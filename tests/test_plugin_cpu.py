@@ -126,3 +126,24 @@ def test_cache_engine_block_size():
     assert eng.dtype == torch.uint8 and len(eng.gpu_cache) == 2
     assert eng.gpu_cache[0].shape == (2, 4, 16 * 2 * 64) and eng.cpu_cache[1].shape == (2, 3, 2048)
     eng.apply(None, torch.empty(0, 2, dtype=torch.int64), None)  # empty worker input: no op calls
+
+
+def test_selector_mirrors_reference(monkeypatch):
+    """selector.py:37-75: AttnBackend.from_engine -> backend instance; unknown names raise."""
+    import types
+    from light_vllm_b200.attention.selector import AttnBackend, _Backend
+    mc = types.SimpleNamespace(get_num_attention_heads=lambda: 32, get_head_size=lambda: 128,
+                               get_num_kv_heads=lambda: 8, get_sliding_window=lambda: None,
+                               dtype=torch.bfloat16)
+    engine = types.SimpleNamespace(engine_config=types.SimpleNamespace(model_config=mc),
+                                   workflow=types.SimpleNamespace(attn_type="DECODER"))
+    monkeypatch.delenv("VLLM_ATTENTION_BACKEND", raising=False)
+    backend = AttnBackend.from_engine(engine)
+    assert backend.get_name() == PagedB200AttentionBackend.get_name()
+    assert AttnBackend.which_attn_to_use(32, 128, 8, None, torch.float16) == _Backend.PAGED_B200
+    monkeypatch.setenv("VLLM_ATTENTION_BACKEND", "FLASH_ATTN")
+    with pytest.raises(ValueError, match="Invalid attention backend"):
+        AttnBackend.which_attn_to_use(32, 128, 8, None, torch.float16)
+    monkeypatch.setenv("VLLM_ATTENTION_BACKEND", "PAGED_B200")
+    with pytest.raises(ValueError, match="Head size"):
+        AttnBackend.which_attn_to_use(32, 100, 8, None, torch.float16)
