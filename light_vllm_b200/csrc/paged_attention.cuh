@@ -234,8 +234,34 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
   // ---------------- online softmax (exp2 domain) ----------------
   float alpha[RS];
   bool changed = false;
+  // FASTSM (prefill fast path, no mask / bias): max over the raw scores, then one FFMA + ex2 per
+  // score (scale > 0, so max(s * scale) = max(s) * scale).
+  constexpr bool FASTSM = PFX && PLAIN && !TAIL && !ROWB;
 #pragma unroll
   for (int rs = 0; rs < RS; ++rs) {
+    if constexpr (FASTSM) {
+      float mx = kNegInf;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) mx = fmaxf(mx, fmaxf(s[nt][2 * rs], s[nt][2 * rs + 1]));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      const float m_new = fmaxf(m[rs], mx * scale_log2);
+      alpha[rs] = fast_exp2(m[rs] - m_new);  // m_new is finite here: nothing is masked
+      changed |= (m_new != m[rs]);
+      m[rs] = m_new;
+      float sum = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const float pv = fast_exp2(fmaf(s[nt][2 * rs + e], scale_log2, -m_new));
+          s[nt][2 * rs + e] = pv;
+          sum += pv;
+        }
+      }
+      l[rs] = l[rs] * alpha[rs] + sum;
+      continue;
+    }
     float mx = kNegInf;
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
@@ -309,6 +335,19 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
       pa2 = pa3 = 0u;
     }
     if constexpr (KV == B200_KV_AUTO && PFX && BS >= 16) {
+      // For q4 >= 2 tile 2kk holds the UPPER token pair of this lane's four tokens.  The k-slot a
+      // fragment sits in is only a label shared by all lanes with the same q4, so the two P
+      // fragments are swapped (4 selects) instead of the V words (2 selects per d-tile).
+      if (q4 & 2) {
+        uint32_t tmp = pa0; pa0 = pa2; pa2 = tmp;
+        tmp = pa1; pa1 = pa3; pa3 = tmp;
+      }
+      uint32_t vm0 = 0xffffffffu, vm1 = 0xffffffffu;
+      if constexpr (TAIL) {
+        const int t0 = kk * 16 + 4 * q4;
+        vm0 = (t0 < valid ? 0x0000ffffu : 0u) | (t0 + 1 < valid ? 0xffff0000u : 0u);
+        vm1 = (t0 + 2 < valid ? 0x0000ffffu : 0u) | (t0 + 3 < valid ? 0xffff0000u : 0u);
+      }
       // V page [D][BS] 16-bit: this lane's P fragments cover tokens 4*q4..4*q4+3 of the 16-token
       // group (page_token<.., true>): one 64-bit load per d-tile, a warp reads 256 contiguous bytes.
       const uint32_t base = v_smem + (uint32_t)((lane >> 2) * BS * 2 + q4 * 8 + (kk % GPP) * 32) +
@@ -317,10 +356,10 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
       for (int j = 0; j < NDT; ++j) {
         uint32_t w0, w1;
         asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(base + (uint32_t)(j * 8 * BS * 2)));
-        uint32_t b0 = (q4 & 2) ? w1 : w0, b1 = (q4 & 2) ? w0 : w1;
+        uint32_t b0 = w0, b1 = w1;
         if constexpr (TAIL) {
-          b0 &= vmask[2 * kk];
-          b1 &= vmask[2 * kk + 1];
+          b0 &= vm0;
+          b1 &= vm1;
         }
         float acc[4] = {o[j][0], o[j][1], RS == 2 ? o[j][2 * (RS - 1)] : 0.f,
                         RS == 2 ? o[j][2 * (RS - 1) + 1] : 0.f};
