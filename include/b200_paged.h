@@ -234,6 +234,10 @@ int64_t b200_get_max_shared_memory_per_block_device_attribute(int64_t device_id)
  *     alibi_slopes [num_heads] float32 or NULL; sliding_window <= 0 disables the window (ignored
  *                  with ALiBi, as in the reference dispatch :713-811)
  *     scale        the reference fixes 1/sqrt(head_size) (:702); passed explicitly here
+ *     kv_scratch   optional device scratch of >= b200_context_attention_scratch_bytes(num_tokens =
+ *                  rows of k/v, ...) bytes, 16-byte aligned: the new k/v are first rewritten into
+ *                  page layout there (one extra launch) and then stream through the same bulk-copy
+ *                  pipeline as the cached context; NULL (or too small) = each CTA stages them itself
  *   Query token i attends all ctx_len cached tokens and new tokens j <= i.
  */
 int b200_context_attention_fwd(
@@ -244,7 +248,10 @@ int b200_context_attention_fwd(
     int64_t q_stride1, int64_t k_stride0, int64_t k_stride1, int64_t v_stride0, int64_t v_stride1,
     int64_t o_stride0, int64_t o_stride1, int64_t kc_block_stride, int64_t kc_head_stride,
     int64_t vc_block_stride, int64_t vc_head_stride, const float* alibi_slopes, int sliding_window,
-    float scale, int dtype, int device, b200_stream_t stream);
+    float scale, void* kv_scratch, int64_t kv_scratch_bytes, int64_t num_tokens, int dtype,
+    int device, b200_stream_t stream);
+int64_t b200_context_attention_scratch_bytes(int64_t num_tokens, int num_seqs, int num_kv_heads,
+                                             int head_size, int block_size);
 
 /*
  * Context-sharded decode (one sequence whose KV pages are spread over several

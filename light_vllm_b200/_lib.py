@@ -51,6 +51,7 @@ ABI_SYMBOLS = (
     "b200_peer_open",
     "b200_peer_close",
     "b200_context_attention_fwd",
+    "b200_context_attention_scratch_bytes",
 )
 
 
@@ -88,7 +89,9 @@ def _load():
         [vp] * 9 + [i32] * 8 + [i64] * 3 + [f32] * 3 + [i32] * 2 +
         [ctypes.POINTER(vp), i32, i32, i32, ctypes.c_uint32, i32, i32, vp])
     lib.b200_context_attention_fwd.argtypes = (
-        [vp] * 10 + [i32] * 7 + [i64] * 12 + [vp, i32, f32, i32, i32, vp])
+        [vp] * 10 + [i32] * 7 + [i64] * 12 + [vp, i32, f32, vp, i64, i64, i32, i32, vp])
+    lib.b200_context_attention_scratch_bytes.restype = ctypes.c_int64
+    lib.b200_context_attention_scratch_bytes.argtypes = [i64, i32, i32, i32, i32]
     lib.b200_ctx_exchange_status.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_int32), i32]
     lib.b200_peer_alloc.argtypes = [ctypes.POINTER(vp), i64, i32]
     lib.b200_peer_free.argtypes = [vp, i32]

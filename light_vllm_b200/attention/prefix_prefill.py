@@ -8,13 +8,15 @@ import torch
 
 from .. import _lib
 
+_SCRATCH = {}  # per (device, stream): uint8 buffer for the staged new-token pages
+
 
 def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: torch.Tensor,
                           k_cache: torch.Tensor, v_cache: torch.Tensor, b_loc: torch.Tensor,
                           b_start_loc: torch.Tensor, b_seq_len: torch.Tensor,
                           b_ctx_len: torch.Tensor, max_input_len: int,
                           alibi_slopes: Optional[torch.Tensor] = None,
-                          sliding_window: Optional[int] = None) -> None:
+                          sliding_window: Optional[int] = None, use_scratch: bool = True) -> None:
     if not q.is_cuda:
         raise RuntimeError("context_attention_fwd: CUDA tensors required (no CPU implementation)")
     if q.dtype not in (torch.float16, torch.bfloat16):
@@ -33,6 +35,13 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
     if alibi_slopes is not None:
         alibi_slopes = alibi_slopes.to(torch.float32).contiguous()
     import ctypes
+    # scratch for the staged mode (new k/v rewritten into page layout; see csrc/prefix_prefill.cu)
+    need = _lib.lib.b200_context_attention_scratch_bytes(k.shape[0], b_seq_len.shape[0], k.shape[1], Lq,
+                                                         v_cache.shape[3])
+    skey = (q.device, torch.cuda.current_stream(q.device).cuda_stream)  # stream-ordered reuse
+    scratch = _SCRATCH.get(skey)
+    if scratch is None or scratch.numel() < need:
+        scratch = _SCRATCH[skey] = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=q.device)
     rc = _lib.lib.b200_context_attention_fwd(
         q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
         b_loc.data_ptr(), b_start_loc.data_ptr(), b_seq_len.data_ptr(), b_ctx_len.data_ptr(),
@@ -41,7 +50,8 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
         o.stride(0), o.stride(1), k_cache.stride(0), k_cache.stride(1), v_cache.stride(0),
         v_cache.stride(1), alibi_slopes.data_ptr() if alibi_slopes is not None else None,
         int(sliding_window) if sliding_window and sliding_window > 0 else 0,
-        ctypes.c_float(1.0 / (Lq ** 0.5)), _lib._DT[q.dtype], q.device.index,
+        ctypes.c_float(1.0 / (Lq ** 0.5)), scratch.data_ptr() if use_scratch else None, scratch.numel(),
+        k.shape[0], _lib._DT[q.dtype], q.device.index,
         torch.cuda.current_stream(q.device).cuda_stream)
     if rc != 0:
         raise RuntimeError(_lib.last_error())

@@ -25,6 +25,7 @@ struct PrefixParams {
   const void *k_cache, *v_cache;
   const int32_t *block_tables, *start_loc, *seq_lens, *ctx_lens;
   const float* alibi_slopes;
+  const unsigned char* kv_scratch;  // new k/v pre-staged as pages (prefix_stage_kv_kernel) or NULL
   int num_heads, num_kv_heads, group, max_blocks_per_seq, sliding_window, tok_tile, num_stages,
       stage_shift;
   int64_t q_s0, q_s1, k_s0, k_s1, v_s0, v_s1, o_s0, o_s1, kc_bs, kc_hs, vc_bs, vc_hs;
@@ -147,31 +148,48 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
     // the whole issue overhead; every warp keeps its own 32-entry block-table window.
     int win0 = 0;
     int tbl = (lane < n) ? bt[lane] : 0;
+    // Staged mode: the new tokens' k/v were rewritten into page layout (one K page + V page per
+    // (slice, kv head), contiguous), so they follow the context pages through the SAME ring:
+    // pages n .. n_all-1 are slices slice0 .. of the new tokens, one bulk copy each.
+    const bool staged = p.kv_scratch != nullptr;
+    const int last_tok = m0 + tile_tokens - 1;  // newest query of this CTA: keys j <= last_tok
+    const int slice0 = W > 0 ? max(0, m0 - W + 1) / BS : 0;
+    const int n_all = n + (staged ? last_tok / BS + 1 - slice0 : 0);
+    const unsigned char* sbase =
+        staged ? p.kv_scratch + (((int64_t)(start / BS) + seq + slice0) * p.num_kv_heads + kvh) * STAGE_BYTES
+               : nullptr;
     auto issue = [&](int i, int s) {  // one warp, all lanes: page i -> stage s
+      const uint32_t bar = full_u32 + 8 * s;
+      const uint32_t dst = ring_u32 + (uint32_t)s * STAGE_BYTES;
+      if (i >= n) {
+        if (elect_one()) {
+          mbar_arrive_expect_tx(bar, STAGE_BYTES);
+          bulk_g2s(dst, sbase + (int64_t)(i - n) * p.num_kv_heads * STAGE_BYTES, STAGE_BYTES, bar, policy);
+        }
+        return;
+      }
       while (i >= win0 + 32) {
         win0 += 32;
         tbl = (win0 + lane < n) ? bt[win0 + lane] : 0;
       }
       const int64_t blk = __shfl_sync(0xffffffffu, tbl, i - win0);
       if (elect_one()) {
-        const uint32_t bar = full_u32 + 8 * s;
-        const uint32_t dst = ring_u32 + (uint32_t)s * STAGE_BYTES;
         mbar_arrive_expect_tx(bar, STAGE_BYTES);
         bulk_g2s(dst, kbase + blk * p.kc_bs * 2, PAGE_BYTES, bar, policy);
         bulk_g2s(dst + PAGE_BYTES, vbase + blk * p.vc_bs * 2, PAGE_BYTES, bar, policy);
       }
     };
     if (warp == 0) {
-      const int pre = min(NS, n);
+      const int pre = min(NS, n_all);
       for (int i = 0; i < pre; ++i) issue(i, i);
     }
     // NS is a power of two: stage of page j = j & (NS - 1), phase parity = (j >> stage_shift) & 1.
     const int smask = NS - 1, sshift = p.stage_shift;
     constexpr bool kPairOk = PLAIN && BS == 16;  // two pages per step on the unmasked fast path
-    int i = 0, i_prev = 0, next_issue = min(NS, n);
-    while (i < n) {
+    int i = 0, i_prev = 0, next_issue = min(NS, n_all);
+    while (i < n_all) {
       // refill the stages every warp left at least one step ago (pages below i_prev)
-      while (next_issue < n && next_issue - NS < i_prev) {
+      while (next_issue < n_all && next_issue - NS < i_prev) {
         const int j = next_issue++;
         if (warp == (j & (kPrefixWarps - 1))) {
           mbar_wait(empty_u32 + 8 * (j & smask), (uint32_t)(((j >> sshift) - 1) & 1));
@@ -179,12 +197,18 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
         }
       }
       const int s = i & smask;
-      const int tok0 = (page0 + i) * BS;
-      const bool pair = kPairOk && W == 0 && i + 1 < n && tok0 + 2 * BS <= ctx;
       const int s1 = (i + 1) & smask;
+      const bool is_new = i >= n;
+      // Position of the page's first key relative to the sequence start, in "key position" units:
+      // context pages start at (page0 + i) * BS, staged slices at ctx + (slice0 + i - n) * BS.
+      const int tok0 = is_new ? ctx + (slice0 + i - n) * BS : (page0 + i) * BS;
+      const int hi_q = ctx + w_tok_hi, lo_q = ctx + w_tok_lo;  // query positions of this warp
+      bool pair = false;
+      if (kPairOk && W == 0 && warp_on && i + 1 < n_all)
+        pair = is_new ? (tok0 + 2 * BS - 1 <= lo_q) : (tok0 + 2 * BS <= ctx);
       mbar_wait(full_u32 + 8 * s, (uint32_t)((i >> sshift) & 1));
       if (pair) mbar_wait(full_u32 + 8 * s1, (uint32_t)(((i + 1) >> sshift) & 1));
-      if (warp_on) {
+      if (warp_on && tok0 <= hi_q) {
         const uint32_t ksm = ring_u32 + (uint32_t)s * STAGE_BYTES;
         int row_lo[RS], row_hi[RS];
         float row_rel0[RS];
@@ -192,11 +216,11 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
         for (int rs = 0; rs < RS; ++rs) {
           const int pos_q = ctx + max(row_tok[rs], 0);
           row_lo[rs] = W > 0 ? pos_q - W + 1 - tok0 : 0;
-          row_hi[rs] = BS;
+          row_hi[rs] = is_new ? pos_q - tok0 + 1 : BS;  // causal frontier inside the new tokens
           row_rel0[rs] = (float)(tok0 - pos_q);
         }
-        const bool tail = tok0 + BS > ctx;
-        const bool windowed = W > 0 && (ctx + w_tok_hi - W + 1 > tok0);
+        const bool tail = !is_new && tok0 + BS > ctx;
+        const bool masked = (W > 0 && (hi_q - W + 1 > tok0)) || (is_new && tok0 + BS - 1 > lo_q);
         if constexpr (kPairOk) {
           if (pair) {
             const uint32_t stride = (uint32_t)(s1 - s) * (uint32_t)STAGE_BYTES;  // wraps for s1 < s
@@ -210,7 +234,7 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
           process_page_ex<T, D, BS, KV, GROWS, true, PLAIN, true, true>(
               ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, ctx - tok0, p.scale_log2, slope, 0.f, row_on,
               row_lo, row_hi, row_rel0);
-        else if (windowed || !PLAIN)
+        else if (masked || !PLAIN)
           process_page_ex<T, D, BS, KV, GROWS, false, PLAIN, true, true>(
               ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS, p.scale_log2, slope, 0.f, row_on, row_lo,
               row_hi, row_rel0);
@@ -230,8 +254,8 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
   }
   __syncthreads();  // the ring becomes the staging area of phase 2
 
-  // =========================== phase 2: new tokens (causal) ===========================
-  {
+  // ============ phase 2 (no scratch given): new tokens staged by the CTA itself ============
+  if (p.kv_scratch == nullptr) {
     const int last_tok = m0 + tile_tokens - 1;  // newest query of this CTA: keys j <= last_tok
     int slice0 = 0;
     if (W > 0) slice0 = max(0, m0 - W + 1) / BS;
@@ -321,6 +345,45 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
   }
 }
 
+// Pre-pass of the staged mode: rewrites the packed new-token k/v of every (sequence, kv head) into
+// page layout -- per BS-token slice one K page [D/8][BS][8] followed by one V page [D][BS], zero
+// filled past the sequence's last new token -- so that the attention kernel can pull them through
+// the same bulk-copy ring as the cached context.  Slice `sl` of sequence b lives at slice index
+// start_loc[b] / BS + b + sl (sequences never overlap: sum of ceil(q/BS) <= start/BS + b).
+// Traffic: 2x the new k/v bytes, a few MB; one launch.
+template <typename T, int D, int BS>
+__global__ void __launch_bounds__(128) prefix_stage_kv_kernel(const __grid_constant__ PrefixParams p,
+                                                              unsigned char* scratch) {
+  constexpr int PAGE_BYTES = D * BS * 2;
+  constexpr int NDT = D / 8;
+  constexpr int VEC_PER_PAGE = BS * NDT;
+  __shared__ __align__(16) unsigned char sm[2 * PAGE_BYTES];
+  const int seq = blockIdx.z, kvh = blockIdx.y, sl = blockIdx.x;
+  const int qlen = p.seq_lens[seq] - p.ctx_lens[seq];
+  const int t0 = sl * BS;
+  if (t0 >= qlen) return;
+  const int64_t start = p.start_loc[seq];
+  const T* kg = static_cast<const T*>(p.k) + (int64_t)kvh * p.k_s1;
+  const T* vg = static_cast<const T*>(p.v) + (int64_t)kvh * p.v_s1;
+  for (int idx = threadIdx.x; idx < VEC_PER_PAGE; idx += blockDim.x) {
+    const int t = idx % BS, c = idx / BS;
+    uint4 kr = make_uint4(0u, 0u, 0u, 0u), vr = kr;
+    if (t0 + t < qlen) {
+      kr = *reinterpret_cast<const uint4*>(kg + (start + t0 + t) * p.k_s0 + c * 8);
+      vr = *reinterpret_cast<const uint4*>(vg + (start + t0 + t) * p.v_s0 + c * 8);
+    }
+    *reinterpret_cast<uint4*>(sm + (size_t)(c * BS + t) * 16) = kr;
+    const uint16_t* e = reinterpret_cast<const uint16_t*>(&vr);
+#pragma unroll
+    for (int x = 0; x < 8; ++x)
+      *reinterpret_cast<uint16_t*>(sm + PAGE_BYTES + (size_t)((c * 8 + x) * BS + t) * 2) = e[x];
+  }
+  __syncthreads();
+  unsigned char* dst = scratch + (((int64_t)(start / BS) + seq + sl) * p.num_kv_heads + kvh) * (2 * PAGE_BYTES);
+  for (int idx = threadIdx.x; idx < 2 * PAGE_BYTES / 16; idx += blockDim.x)
+    reinterpret_cast<uint4*>(dst)[idx] = reinterpret_cast<const uint4*>(sm)[idx];
+}
+
 namespace {
 
 template <int D, int BS>
@@ -349,6 +412,12 @@ int launch_prefix(PrefixParams& p, int num_seqs, int max_query_len, int device, 
   if (!configured[plain][slot].load(std::memory_order_acquire)) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     configured[plain][slot].store(1, std::memory_order_release);
+  }
+  if (p.kv_scratch != nullptr) {
+    dim3 sgrid((max_query_len + BS - 1) / BS, p.num_kv_heads, num_seqs);
+    prefix_stage_kv_kernel<T, D, BS><<<sgrid, 128, 0, stream>>>(p, const_cast<unsigned char*>(p.kv_scratch));
+    count_launch();
+    B200_CUDA_OK(cudaGetLastError());
   }
   const int tiles = (max_query_len + p.tok_tile - 1) / p.tok_tile;
   B200_CHECK_ARG(p.num_kv_heads <= 65535 && num_seqs <= 65535, "context_attention_fwd: grid too large");
@@ -387,6 +456,13 @@ int dispatch_prefix(PrefixParams& p, int head_size, int block_size, int num_seqs
 
 using namespace b200;
 
+extern "C" int64_t b200_context_attention_scratch_bytes(int64_t num_tokens, int num_seqs,
+                                                        int num_kv_heads, int head_size,
+                                                        int block_size) {
+  if (num_tokens < 0 || num_seqs < 0 || block_size <= 0) return -1;
+  return (num_tokens / block_size + num_seqs + 1) * (int64_t)num_kv_heads * 2 * head_size * block_size * 2;
+}
+
 extern "C" int b200_context_attention_fwd(
     const void* q, const void* k, const void* v, void* out, const void* key_cache,
     const void* value_cache, const int32_t* block_tables, const int32_t* start_loc,
@@ -395,7 +471,8 @@ extern "C" int b200_context_attention_fwd(
     int64_t q_stride1, int64_t k_stride0, int64_t k_stride1, int64_t v_stride0, int64_t v_stride1,
     int64_t o_stride0, int64_t o_stride1, int64_t kc_block_stride, int64_t kc_head_stride,
     int64_t vc_block_stride, int64_t vc_head_stride, const float* alibi_slopes, int sliding_window,
-    float scale, int dtype, int device, b200_stream_t stream) {
+    float scale, void* kv_scratch, int64_t kv_scratch_bytes, int64_t num_tokens, int dtype,
+    int device, b200_stream_t stream) {
   B200_CHECK_ARG(num_seqs >= 0 && max_query_len >= 0 && head_size > 0 && block_size > 0,
                  "context_attention_fwd: bad sizes");
   if (num_seqs == 0 || max_query_len == 0) return B200_OK;
@@ -429,6 +506,13 @@ extern "C" int b200_context_attention_fwd(
   p.v_s0 = v_stride0; p.v_s1 = v_stride1; p.o_s0 = o_stride0; p.o_s1 = o_stride1;
   p.kc_bs = kc_block_stride; p.kc_hs = kc_head_stride; p.vc_bs = vc_block_stride; p.vc_hs = vc_head_stride;
   p.scale_log2 = scale * 1.4426950408889634f;
+  // staged mode needs room for num_tokens / block_size + num_seqs + 1 slices of every kv head
+  const int64_t need = b200_context_attention_scratch_bytes(num_tokens, num_seqs, num_kv_heads, head_size,
+                                                            block_size);
+  p.kv_scratch = (kv_scratch != nullptr && kv_scratch_bytes >= need &&
+                  (reinterpret_cast<uintptr_t>(kv_scratch) & 15) == 0)
+                     ? static_cast<const unsigned char*>(kv_scratch)
+                     : nullptr;
   if (dtype == B200_DT_F16)
     return dispatch_prefix<__half>(p, head_size, block_size, num_seqs, max_query_len, dev, (cudaStream_t)stream);
   return dispatch_prefix<__nv_bfloat16>(p, head_size, block_size, num_seqs, max_query_len, dev, (cudaStream_t)stream);

@@ -81,11 +81,13 @@ def test_oracle_edge_cases(oracle):
 
 
 # ---------------------------------------------------------------- product path (GPU) ----
-def _gpu(c, slopes=None, window=0):
+def _gpu(c, slopes=None, window=0, use_scratch=True):
+    import functools
     from light_vllm_b200.attention.prefix_prefill import context_attention_fwd
     d = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in c.items()}
     out = torch.full_like(d["query"], float("nan"))
-    _call(context_attention_fwd, d, out, slopes.cuda() if slopes is not None else None, window)
+    _call(functools.partial(context_attention_fwd, use_scratch=use_scratch), d, out,
+          slopes.cuda() if slopes is not None else None, window)
     torch.cuda.synchronize()
     return out.cpu()
 
@@ -190,3 +192,16 @@ def test_plugin_prefix_prefill_then_decode(oracle):
     v = c["value"].reshape(T, KH * D).to(dev)
     out = impl.forward(q, k, v, kv_cache, meta).view(T, H, D).cpu()
     assert (out.double() - ground_truth(c)).abs().max().item() <= 2e-3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("window", [0, 9])
+@pytest.mark.parametrize("H,KH,D,BS", [(32, 8, 128, 16), (6, 2, 120, 8), (4, 2, 192, 32)])
+def test_kernel_without_scratch_stages_in_cta(oracle, window, H, KH, D, BS):
+    """kv_scratch = NULL: every CTA stages the new k/v itself (the other mode is the default)."""
+    c = make_prefix_case([0, 129, 40], [70, 64, 5], H, KH, D, BS, torch.float16, seed=77)
+    want = _call(oracle.context_attention_fwd, c, torch.zeros_like(c["query"]), None, window)
+    a = _gpu(c, None, window, use_scratch=False)
+    b = _gpu(c, None, window, use_scratch=True)
+    assert (a.float() - want.float()).abs().max().item() <= 2e-3
+    assert (b.float() - want.float()).abs().max().item() <= 2e-3

@@ -35,6 +35,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--dtype", default="bfloat16")
+    ap.add_argument("--no-scratch", action="store_true", help="CTA-local staging of the new k/v")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     dtype = getattr(torch, a.dtype)
@@ -56,7 +57,8 @@ def main():
     out = torch.empty_like(q)
 
     def ours():
-        context_attention_fwd(q, k, v, out, kc, vc, bt, start[:-1], seq, cl, ql, None, None)
+        context_attention_fwd(q, k, v, out, kc, vc, bt, start[:-1], seq, cl, ql, None, None,
+                              use_scratch=not a.no_scratch)
 
     # library baseline: contiguous K/V per sequence (context gathered from the pages + new tokens)
     nctx = (ctx + BS - 1) // BS
@@ -104,7 +106,7 @@ def main():
         "kv_bytes_algorithmic": kv_bytes, "kv_GBps_algorithmic": round(kv_bytes / ms / 1e6, 1),
         "sdpa_library_ms": round(ms_sdpa, 4), "speedup_vs_sdpa": round(ms_sdpa / ms, 3),
         "max_abs_vs_sdpa": err, "gpu_launches": int(launches), "steps": a.steps, "warmup": a.warmup,
-        "dtype": a.dtype,
+        "dtype": a.dtype, "staged_new_kv": not a.no_scratch,
         "config": {"workload": f"{B} seqs x (ctx {ctx} cached + {ql} new tokens), H{H}/KH{KH}/D{D}/BS{BS}"}}),
         flush=True)
 
