@@ -268,7 +268,9 @@ int64_t b200_context_attention_scratch_bytes(int64_t num_tokens, int num_seqs, i
  *     exchange_bufs [world] host array: this process's addresses of every rank's exchange buffer
  *                   (own buffer from b200_peer_alloc, peers' from b200_peer_open)
  *     max_pairs     (seq, head) capacity the buffers were sized for (b200_ctx_exchange_bytes)
- *     epoch         1, 2, 3, ... incremented by the caller on every call, same on all ranks
+ *     epoch         1, 2, 3, ... incremented by the caller on every call, same on all ranks; or 0 on
+ *                   every rank = device-managed (a counter in the exchange buffer, advanced by the
+ *                   merge phase), which is what lets the call be captured in a CUDA graph
  *     phases        3 = partition pass, then publish + wait + merge in one kernel (the normal call);
  *                   1 = partition pass + publish only, 2 = wait + merge only (same epoch): a
  *                   split-phase form that lets the caller put other work between the two

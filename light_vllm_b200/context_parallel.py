@@ -109,6 +109,8 @@ class ContextShardGroup:
         self._opened = opened
         self._owns = owns
         self.epoch = 0
+        # True: the epoch lives in the exchange buffer (CUDA-graph capturable); all ranks must agree
+        self.device_epoch = True
         self._scratch = {}
 
     # ---- construction ----
@@ -192,7 +194,7 @@ class ContextShardGroup:
         if kv < 0:
             raise RuntimeError(f"Unsupported data type of kv cache: {kv_cache_dtype}")
         if phases != 2:
-            self.epoch += 1
+            self.epoch += 1  # calls issued (the kernels keep the protocol epoch on the device)
         f = ctypes.c_float
         rc = _lib.lib.b200_paged_attention_ctx_shard(
             out.data_ptr(), es.data_ptr(), ml.data_ptr(), tmp.data_ptr(), query.data_ptr(),
@@ -200,7 +202,7 @@ class ContextShardGroup:
             local_seq_lens.data_ptr(), B, H, num_kv_heads, D, block_size, int(max_local_seq_len),
             block_tables.shape[1], es.shape[2], query.stride(0), key_cache.stride(0),
             key_cache.stride(1), f(scale), f(k_scale), f(v_scale), _lib._DT[query.dtype], kv,
-            self._bufs, self.rank, self.world, self.max_pairs, self.epoch & 0xFFFFFFFF, phases,
+            self._bufs, self.rank, self.world, self.max_pairs, 0 if self.device_epoch else (self.epoch & 0xFFFFFFFF), phases,
             query.device.index if query.device.index is not None else torch.cuda.current_device(),
             torch.cuda.current_stream(query.device).cuda_stream)
         _check(rc)

@@ -16,6 +16,7 @@
 // n+1 cannot finish before every peer has published call n+1, which it does after reading call n.
 #include "paged_attention.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 namespace b200 {
@@ -50,17 +51,29 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
                           int total_pairs, const __grid_constant__ CtxPeers peers, int rank,
                           int world, int max_pairs, uint32_t epoch, int phases,
                           long long timeout_cycles) {
-  extern __shared__ float wsm[];  // [4 warps][weights_stride]
+  extern __shared__ float wsm[];  // [4 warps][head_size] partial folds
+  __shared__ uint32_t epoch_s;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
+  // epoch == 0: device-managed.  The call's epoch is the counter in this rank's own header + 1; the
+  // last CTA to finish the merge phase advances it, so that a CUDA graph holding this launch can be
+  // replayed (a host-supplied epoch would be frozen into the graph).
+  uint32_t* hdr_epoch = reinterpret_cast<uint32_t*>(peers.buf[rank]) + world * kCtxMaxCtas + 1;
+  const bool device_epoch = epoch == 0;
+  if (threadIdx.x == 0) epoch_s = device_epoch ? __ldcg(hdr_epoch) + 1u : epoch;
+  __syncthreads();
+  epoch = epoch_s;
   const int row_floats = head_size + kCtxRowPad;
   const size_t hdr = ctx_header_bytes(world);
   const size_t slot_floats = (size_t)world * max_pairs * row_floats;
   const size_t slot_off = (size_t)(epoch & 1u) * slot_floats;
 
   // ---- phase 1: fold my partitions, publish the triple to every rank (incl. myself) ----
-  float* w = wsm + warp * weights_stride;
-  for (int pair = blockIdx.x * 4 + warp; (phases & 1) && pair < total_pairs; pair += gridDim.x * 4) {
+  // One CTA per (seq, head) pair: every warp derives the pair's (max, sum) from the partition
+  // statistics, the four warps fold interleaved quarters of the partitions (independent loads,
+  // short dependency chains) into shared memory, and the CTA stores the normalised row to the peers.
+  float* part = wsm;  // [4 warps][head_size]
+  for (int pair = blockIdx.x; (phases & 1) && pair < total_pairs; pair += gridDim.x) {
     const int seq = pair / num_heads;
     const int seq_len = seq_lens[seq];
     const int np = (seq_len + partition_tokens - 1) / partition_tokens;
@@ -72,36 +85,32 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
 #pragma unroll
     for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
     float sum = 0.f;
-    for (int j = lane; j < np; j += 32) {
-      const float r = (mx == kNegInf) ? 0.f : es[j] * expf(ml[j] - mx);
-      w[j] = r;
-      sum += r;
-    }
+    for (int j = lane; j < np; j += 32) sum += (mx == kNegInf) ? 0.f : es[j] * expf(ml[j] - mx);
 #pragma unroll
     for (int s = 16; s >= 1; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
     const float inv = sum > 0.f ? __fdividef(1.f, sum) : 0.f;
-    __syncwarp();
-    const size_t row_off = slot_off + ((size_t)rank * max_pairs + pair) * row_floats;
     for (int d0 = 2 * lane; d0 < head_size; d0 += 64) {
       float a0 = 0.f, a1 = 0.f;
-#pragma unroll 8
-      for (int j = 0; j < np; ++j) {  // independent loads: unrolled so that they overlap
-        const float wj = w[j] * inv;
+#pragma unroll 4
+      for (int j = warp; j < np; j += 4) {
+        const float wj = es[j] * expf(ml[j] - mx);
         a0 += to_f32<T>(t[(int64_t)j * head_size + d0]) * wj;
         a1 += to_f32<T>(t[(int64_t)j * head_size + d0 + 1]) * wj;
       }
-      for (int r = 0; r < world; ++r) {
-        float* dst = reinterpret_cast<float*>(peers.buf[r] + hdr) + row_off;
-        *reinterpret_cast<float2*>(dst + kCtxRowPad + d0) = make_float2(a0, a1);
-      }
+      *reinterpret_cast<float2*>(part + warp * head_size + d0) = make_float2(a0, a1);
     }
-    if (lane == 0) {
-      for (int r = 0; r < world; ++r) {
-        float* dst = reinterpret_cast<float*>(peers.buf[r] + hdr) + row_off;
-        *reinterpret_cast<float2*>(dst) = make_float2(mx, sum);
-      }
+    __syncthreads();
+    const size_t row_off = slot_off + ((size_t)rank * max_pairs + pair) * row_floats;
+    for (int d = threadIdx.x; d < head_size; d += blockDim.x) {
+      const float v = (part[d] + part[head_size + d] + part[2 * head_size + d] + part[3 * head_size + d]) * inv;
+      for (int r = 0; r < world; ++r)
+        reinterpret_cast<float*>(peers.buf[r] + hdr)[row_off + kCtxRowPad + d] = v;
     }
-    __syncwarp();  // w[] is reused by the next pair
+    if (threadIdx.x == 0) {
+      for (int r = 0; r < world; ++r)
+        *reinterpret_cast<float2*>(reinterpret_cast<float*>(peers.buf[r] + hdr) + row_off) = make_float2(mx, sum);
+    }
+    __syncthreads();  // part[] is reused by the next pair
   }
   __threadfence_system();
   __syncthreads();
@@ -126,7 +135,7 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
   }
   __syncthreads();
   const float* data = reinterpret_cast<const float*>(mine + hdr) + slot_off;
-  for (int pair = blockIdx.x * 4 + warp; pair < total_pairs; pair += gridDim.x * 4) {
+  for (int pair = blockIdx.x; pair < total_pairs; pair += gridDim.x) {
     float M = kNegInf;
     for (int r = 0; r < world; ++r) {
       const float2 st = __ldcg(reinterpret_cast<const float2*>(data + ((size_t)r * max_pairs + pair) * row_floats));
@@ -139,20 +148,26 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
     }
     const float inv = __fdividef(1.f, S + 1e-6f);
     T* o = out + (int64_t)pair * head_size;
-    for (int d0 = 2 * lane; d0 < head_size; d0 += 64) {
-      float a0 = 0.f, a1 = 0.f;
+    for (int d = threadIdx.x; d < head_size; d += blockDim.x) {
+      float acc = 0.f;
       for (int r = 0; r < world; ++r) {
         const float* row = data + ((size_t)r * max_pairs + pair) * row_floats;
         const float2 st = __ldcg(reinterpret_cast<const float2*>(row));
-        if (st.y > 0.f) {
-          const float wr = st.y * expf(st.x - M) * inv;
-          const float2 v = __ldcg(reinterpret_cast<const float2*>(row + kCtxRowPad + d0));
-          a0 += v.x * wr;
-          a1 += v.y * wr;
-        }
+        if (st.y > 0.f) acc += __ldcg(row + kCtxRowPad + d) * (st.y * expf(st.x - M) * inv);
       }
-      o[d0] = from_f32<T>(a0);
-      o[d0 + 1] = from_f32<T>(a1);
+      o[d] = from_f32<T>(acc);
+    }
+  }
+  if (device_epoch) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned int* done = reinterpret_cast<unsigned int*>(hdr_epoch) + 1;
+      __threadfence();
+      if (atomicAdd(done, 1u) == gridDim.x - 1) {  // every CTA of this launch has read hdr_epoch
+        *done = 0u;
+        *hdr_epoch = epoch;
+        __threadfence();
+      }
     }
   }
 }
@@ -174,10 +189,12 @@ int launch_ctx_exchange(void* out, const float* exp_sums, const float* max_logit
     B200_CHECK_ARG(exchange_bufs && exchange_bufs[r], "ctx_shard: exchange buffer of rank %d is null", r);
     peers.buf[r] = static_cast<unsigned char*>(exchange_bufs[r]);
   }
-  int blocks = (int)((pairs + 3) / 4);
-  if (blocks > 148) blocks = 148;  // same on every rank (flags are per CTA); all co-resident
-  const int wstride = (parts + 3) & ~3;
-  const size_t wsmem = (size_t)4 * wstride * sizeof(float);
+  int blocks = (int)pairs;
+  static const int cap = [] { const char* e = getenv("B200_CTX_MAX_CTAS"); int v = e ? atoi(e) : 0; return v > 0 && v <= kCtxMaxCtas ? v : 148; }();
+  if (blocks > cap) blocks = cap;  // same on every rank (flags are per CTA); all co-resident
+  const int wstride = head_size;
+  const size_t wsmem = (size_t)4 * head_size * sizeof(float);
+  (void)parts;
   const long long timeout = 4000000000LL;  // ~2 s of SM clocks: a missing peer must not hang the GPU
 #define B200_CTX_LAUNCH(T)                                                                       \
   ctx_exchange_merge_kernel<T><<<blocks, 128, wsmem, stream>>>(                                  \

@@ -149,11 +149,11 @@ def _run_virtual(case, world, chunk, calls=1, kv_cache_dtype="auto", k_scale=1.0
     outs = [torch.full_like(d["query"], float("nan")) for _ in range(world)]
     torch.cuda.synchronize()
     try:
-        # Virtual ranks share one device, and CUDA may put two of their streams on one hardware
-        # queue: a fused publish+wait kernel queued ahead of a peer's publish would then wait for
-        # work stuck behind itself.  So more than two virtual ranks use the split-phase form
-        # (every publish is queued before any wait); real one-process-per-GPU ranks and the
-        # two-rank case run the fused kernel.
+        # Virtual ranks share ONE device: a fused publish+wait kernel of one rank spins until the
+        # other rank's kernels have run, and those may be queued behind it (shared hardware queue)
+        # or be denied the SMs it occupies (observed with a 148-CTA exchange grid).  So virtual
+        # ranks use the split-phase form -- every publish is queued before any wait; the fused
+        # kernel is exercised by the real one-process-per-GPU ranks (test_two_gpu_ipc_ranks).
         for _ in range(calls):
             for ph in ((3,) if fused else (1, 2)):
                 for r in range(world):
@@ -178,7 +178,7 @@ def test_virtual_ranks_match_oracle(oracle, dtype, tol, world, chunk):
     lens = [1, 15, 33, 700, 2049, 0, 5000]
     case = make_case(len(lens), 32, 8, 128, 16, lens, dtype, seed=21, nan_padding=True)
     want = _oracle_out(oracle, case).float()
-    outs = _run_virtual(case, world, chunk, calls=3, fused=(world == 2))  # 3 calls: both data slots
+    outs = _run_virtual(case, world, chunk, calls=3)  # 3 calls: both data slots + epoch reuse
     for r, o in enumerate(outs):
         err = (o.float() - want).abs().max().item()
         assert err <= tol, f"rank {r}: max-abs {err}"
@@ -237,7 +237,7 @@ def _ipc_worker(rank, world, port, tmpdir):
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        lens = [3000, 17, 9000, 0]
+        lens = [3000, 17, 9000, 0, 700]  # 160 (seq, head) pairs: more than the 148-CTA exchange grid
         case = make_case(len(lens), 32, 8, 128, 16, lens, torch.float16, seed=8)
         sh = ContextSharding(world, 16, 4)
         bt, ll, mx = sh.shard_batch(case["block_tables"], lens, rank)
@@ -250,6 +250,21 @@ def _ipc_worker(rank, world, port, tmpdir):
                                 bt.to(dev), ll.to(dev), 16, mx)
         torch.cuda.synchronize()
         assert grp.status() == 0
+        # the same call replayed from a CUDA graph (device-managed epochs)
+        dist.barrier()
+        first = out.clone()
+        out.fill_(float("nan"))
+        graph = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(dev)
+        btd, lld = bt.to(dev), ll.to(dev)
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(graph, stream=side):
+                grp.paged_attention(out, d["query"], d["key_cache"], d["value_cache"], 8,
+                                    case["scale"], btd, lld, 16, mx)
+        for _ in range(3):
+            graph.replay()
+        torch.cuda.synchronize()
+        assert grp.status() == 0 and torch.equal(out, first)
         want = torch.empty_like(case["query"])
         oracle.paged_attention_v1(want, case["query"], case["key_cache"], case["value_cache"], 8,
                                   case["scale"], case["block_tables"], case["seq_lens"], 16,

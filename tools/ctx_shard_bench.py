@@ -38,6 +38,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--chunk-blocks", type=int, default=4)
     ap.add_argument("--local", type=int, default=0, help="N virtual ranks on one GPU")
+    ap.add_argument("--graph", action="store_true",
+                    help="replay each step (one per layer pool) from a CUDA graph (one-process-per-GPU mode)")
     a = ap.parse_args()
 
     H, KH, D, BS = 32, 8, 128, 16
@@ -135,11 +137,31 @@ def main():
         for s in streams:
             cur.wait_stream(s)
 
-    shard_ms = timed(shard_step, a.steps, a.warmup)
+    step_fn = shard_step
+    if a.graph and distributed:
+        # device-managed epochs make the sharded call graph-capturable: one graph per layer pool
+        for i in range(a.layers):
+            shard_step(i)
+        torch.cuda.synchronize()
+        dist.barrier()
+        graphs = []
+        side = torch.cuda.Stream(dev)
+        for i in range(a.layers):
+            g_ = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(side):
+                with torch.cuda.graph(g_, stream=side):
+                    shard_step(i)
+            graphs.append(g_)
+        torch.cuda.synchronize()
+        dist.barrier()
+
+        def step_fn(i):
+            graphs[i % a.layers].replay()
+    shard_ms = timed(step_fn, a.steps, a.warmup)
     status = [grp.status() for grp in groups]
     # same pool for the comparison
     base_step(0)
-    shard_step(0)
+    step_fn(0)
     torch.cuda.synchronize()
     err = max((o.float() - out_ref.float()).abs().max().item() for o in outs)
     if distributed:
@@ -150,6 +172,7 @@ def main():
         print(json.dumps({
             "metric": "ctx_sharded_decode_kv_read_GBps", "unit": "GB/s", "n_gpus": world if distributed else 1,
             "virtual_ranks": 0 if distributed else world, "scaling": "strong",
+            "cuda_graph": bool(a.graph and distributed),
             "value": round(kv_bytes / shard_ms / 1e6, 1), "ms_per_step": round(shard_ms, 4),
             "single_gpu_ms_per_step": round(base_ms, 4),
             "single_gpu_GBps": round(kv_bytes / base_ms / 1e6, 1),
