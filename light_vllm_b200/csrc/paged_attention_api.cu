@@ -36,9 +36,9 @@ struct CtxShardArgs {
 // ---------------------------------------------------------------------------------------
 // v2 merge: out = sum_j tmp_out_j * exp_sum_j * e^(m_j - m) / (sum_j exp_sum_j e^(m_j - m) + 1e-6)
 // (reference: paged_attention_v2_reduce_kernel, attention_kernels.cu:565-669, one 128-thread CTA
-// per (seq, head)).  Here: one warp per (seq, head), 4 pairs per CTA; the lanes first turn the
-// partition statistics into normalised weights held in shared memory, then stream tmp_out with
-// 4-byte loads, partitions outermost so every load is one coalesced row.
+// per (seq, head)).  Here: also one CTA per (seq, head); the weights go to shared memory, the four
+// warps fold interleaved quarters of the partitions (coalesced 4-byte row loads, four short
+// chains instead of one long one) and the CTA adds the partial rows.
 // `partition_tokens` is the context length one partition covers (a multiple of 512 chosen by
 // make_plan; the scratch tensors' partition stride stays max_num_partitions).
 // ---------------------------------------------------------------------------------------
@@ -49,48 +49,56 @@ paged_attention_v2_reduce_kernel(T* __restrict__ out, const float* __restrict__ 
                                  const T* __restrict__ tmp_out, const int32_t* __restrict__ seq_lens,
                                  int num_heads, int head_size, int max_num_partitions,
                                  int partition_tokens, int weights_stride, int64_t total_pairs) {
-  extern __shared__ float wsm[];  // [4 warps][weights_stride]
+  // One CTA per (seq, head): all warps derive the weights (shared memory), then the four warps fold
+  // interleaved quarters of the partitions -- independent coalesced row loads, short dependency
+  // chains -- and the CTA adds the four partial rows.
+  extern __shared__ float wsm[];  // [weights_stride] weights + [4][head_size] partial rows
+  float* w = wsm;
+  float* part = wsm + weights_stride;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  const int64_t pair = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
-  if (pair >= total_pairs) return;
-  const int seq = (int)(pair / num_heads);
-  const int seq_len = seq_lens[seq];
-  const int np = (seq_len + partition_tokens - 1) / partition_tokens;
-  T* o = out + pair * head_size;
-  const T* t = tmp_out + pair * max_num_partitions * head_size;
-  if (np <= 1) {
-    // np == 1: plain copy (attention_kernels.cu:582-594).  np == 0 (empty sequence): the
-    // partition kernel wrote nothing; define the output as zeros.
-    for (int d = lane; d < head_size; d += 32) o[d] = np == 1 ? t[d] : from_f32<T>(0.f);
-    return;
-  }
-  const float* ml = max_logits + pair * max_num_partitions;
-  const float* es = exp_sums + pair * max_num_partitions;
-  float* w = wsm + warp * weights_stride;
-  float mx = -__builtin_huge_valf();
-  for (int j = lane; j < np; j += 32) mx = fmaxf(mx, ml[j]);
-#pragma unroll
-  for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
-  float sum = 0.f;
-  for (int j = lane; j < np; j += 32) {
-    const float r = es[j] * expf(ml[j] - mx);
-    w[j] = r;
-    sum += r;
-  }
-#pragma unroll
-  for (int s = 16; s >= 1; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
-  const float inv = __fdividef(1.f, sum + 1e-6f);
-  __syncwarp();
-  for (int d0 = 2 * lane; d0 < head_size; d0 += 64) {  // head sizes are even
-    float a0 = 0.f, a1 = 0.f;
-    for (int j = 0; j < np; ++j) {
-      const float wj = w[j] * inv;
-      a0 += to_f32<T>(t[(int64_t)j * head_size + d0]) * wj;
-      a1 += to_f32<T>(t[(int64_t)j * head_size + d0 + 1]) * wj;
+  for (int64_t pair = blockIdx.x; pair < total_pairs; pair += gridDim.x) {
+    const int seq = (int)(pair / num_heads);
+    const int seq_len = seq_lens[seq];
+    const int np = (seq_len + partition_tokens - 1) / partition_tokens;
+    T* o = out + pair * head_size;
+    const T* t = tmp_out + pair * max_num_partitions * head_size;
+    if (np <= 1) {
+      // np == 1: plain copy (attention_kernels.cu:582-594).  np == 0 (empty sequence): the
+      // partition kernel wrote nothing; define the output as zeros.
+      for (int d = threadIdx.x; d < head_size; d += blockDim.x) o[d] = np == 1 ? t[d] : from_f32<T>(0.f);
+      continue;
     }
-    o[d0] = from_f32<T>(a0);
-    o[d0 + 1] = from_f32<T>(a1);
+    const float* ml = max_logits + pair * max_num_partitions;
+    const float* es = exp_sums + pair * max_num_partitions;
+    float mx = -__builtin_huge_valf();
+    for (int j = lane; j < np; j += 32) mx = fmaxf(mx, ml[j]);
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+    float sum = 0.f;
+    for (int j = lane; j < np; j += 32) {
+      const float r = es[j] * expf(ml[j] - mx);
+      if (warp == 0) w[j] = r;
+      sum += r;
+    }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
+    const float inv = __fdividef(1.f, sum + 1e-6f);
+    __syncthreads();
+    for (int d0 = 2 * lane; d0 < head_size; d0 += 64) {  // head sizes are even
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll 4
+      for (int j = warp; j < np; j += 4) {
+        const float wj = w[j];
+        a0 += to_f32<T>(t[(int64_t)j * head_size + d0]) * wj;
+        a1 += to_f32<T>(t[(int64_t)j * head_size + d0 + 1]) * wj;
+      }
+      *reinterpret_cast<float2*>(part + warp * head_size + d0) = make_float2(a0, a1);
+    }
+    __syncthreads();
+    for (int d = threadIdx.x; d < head_size; d += blockDim.x)
+      o[d] = from_f32<T>((part[d] + part[head_size + d] + part[2 * head_size + d] + part[3 * head_size + d]) * inv);
+    __syncthreads();  // w[] and part[] are reused by the next pair
   }
 }
 
@@ -351,9 +359,10 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
                                ctx->epoch, ctx->phases, stream);
   if (split_v2) {
     const int64_t pairs = (int64_t)num_seqs * num_heads;
-    const unsigned blocks = (unsigned)((pairs + 3) / 4);
+    const int64_t cap = (int64_t)pl.num_sms * 8;  // grid-stride beyond eight CTAs per SM
+    const unsigned blocks = (unsigned)(pairs < cap ? pairs : cap);
     const int wstride = (pl.v2_parts + 3) & ~3;
-    const size_t wsmem = (size_t)4 * wstride * sizeof(float);
+    const size_t wsmem = ((size_t)wstride + (size_t)4 * head_size) * sizeof(float);
     if (q_dtype == B200_DT_F16)
       paged_attention_v2_reduce_kernel<__half><<<blocks, 128, wsmem, stream>>>(
           static_cast<__half*>(out), exp_sums, max_logits, static_cast<const __half*>(tmp_out),
