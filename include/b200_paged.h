@@ -224,7 +224,8 @@ int64_t b200_get_max_shared_memory_per_block_device_attribute(int64_t device_id)
  *   (light_vllm/decoding/backends/attention/ops/prefix_prefill.py:674-811; caller
  *   ops/paged_attn.py:193-225): prefill of new tokens whose sequence already has ctx_len tokens in
  *   the paged cache (prefix-cache hit, chunked prefill).
- *     q / out      [num_tokens, num_heads, head_size]     T (fp16 | bf16), strides *_stride0/1
+ *     q / out      [num_tokens, num_heads, head_size]     T (fp16 | bf16 on the tensor-core kernel,
+ *                  fp32 on a CUDA-core compatibility kernel), strides *_stride0/1
  *     k / v        [num_tokens, num_kv_heads, head_size]  T: the NEW tokens, packed per sequence
  *     key_cache    [num_blocks, num_kv_heads, head_size/x, block_size, x], value_cache
  *                  [num_blocks, num_kv_heads, head_size, block_size]  T (the reference kernel has no

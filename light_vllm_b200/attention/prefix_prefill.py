@@ -19,8 +19,8 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
                           sliding_window: Optional[int] = None, use_scratch: bool = True) -> None:
     if not q.is_cuda:
         raise RuntimeError("context_attention_fwd: CUDA tensors required (no CPU implementation)")
-    if q.dtype not in (torch.float16, torch.bfloat16):
-        raise RuntimeError(f"Unsupported data type: context_attention_fwd runs fp16 / bf16, got {q.dtype}")
+    if q.dtype not in (torch.float16, torch.bfloat16, torch.float32):
+        raise RuntimeError(f"Unsupported data type: context_attention_fwd runs fp32 / fp16 / bf16, got {q.dtype}")
     if k_cache.dtype != q.dtype or v_cache.dtype != q.dtype:
         raise RuntimeError("context_attention_fwd: the cache must hold the query dtype "
                            "(the reference kernel has no fp8 path)")

@@ -384,6 +384,114 @@ __global__ void __launch_bounds__(128) prefix_stage_kv_kernel(const __grid_const
     reinterpret_cast<uint4*>(dst)[idx] = reinterpret_cast<const uint4*>(sm)[idx];
 }
 
+// float32 prefix prefill (the reference accepts fp32 q/k/v and caches with x = 4, halving its tile,
+// prefix_prefill.py:690-693).  Compatibility path on the CUDA cores, exact fp32 products: one warp per
+// (query token, head); 32 keys per round -- each lane owns one key for Q.K^T (16-byte loads; cached
+// keys of a page are consecutive 16-byte rows), the warp takes the online-softmax step, then the
+// lanes switch to owning d = lane + 32 i for P.V with the probabilities broadcast by shuffle.
+__global__ void __launch_bounds__(128)
+context_attention_f32_kernel(const __grid_constant__ PrefixParams p, int head_size, int block_size,
+                             float scale) {
+  extern __shared__ __align__(16) float q_s[];  // [4 warps][head_size]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int seq = blockIdx.z, head = blockIdx.y;
+  const int ctx = p.ctx_lens[seq];
+  const int qlen = p.seq_lens[seq] - ctx;
+  const int i = blockIdx.x * 4 + warp;
+  if (i >= qlen) return;
+  const int D = head_size, BS = block_size;
+  const int kvh = head / p.group;
+  const int64_t start = p.start_loc[seq];
+  const int pos_q = ctx + i;
+  const float* q = static_cast<const float*>(p.q) + (start + i) * p.q_s0 + (int64_t)head * p.q_s1;
+  float* qs = q_s + warp * D;
+  for (int d = lane; d < D; d += 32) qs[d] = q[d];
+  __syncwarp();
+  const float* kc = static_cast<const float*>(p.k_cache) + (int64_t)kvh * p.kc_hs;
+  const float* vc = static_cast<const float*>(p.v_cache) + (int64_t)kvh * p.vc_hs;
+  const float* kn = static_cast<const float*>(p.k) + (int64_t)kvh * p.k_s1;
+  const float* vn = static_cast<const float*>(p.v) + (int64_t)kvh * p.v_s1;
+  const int32_t* bt = p.block_tables + (int64_t)seq * p.max_blocks_per_seq;
+  const float slope = p.alibi_slopes ? p.alibi_slopes[head] : 0.f;
+  const int W = p.sliding_window;
+  const int n = pos_q + 1;  // visible keys: positions 0 .. pos_q
+  int first = 0;
+  if (W > 0) first = max(0, pos_q - W + 1) & ~31;
+  float acc[8];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) acc[u] = 0.f;
+  float m = kNegInf, l = 0.f;
+  for (int g0 = first; g0 < n; g0 += 32) {
+    const int key = g0 + lane;
+    const bool vis = key < n && !(W > 0 && pos_q - key >= W);
+    int64_t blk = 0;
+    float logit = kNegInf;
+    if (key < n) {
+      float dot = 0.f;
+      if (key < ctx) {
+        blk = bt[key / BS];
+        const float* base = kc + blk * p.kc_bs + (int64_t)(key % BS) * 4;
+        for (int c = 0; c < D / 4; ++c) {
+          const float4 kv = *reinterpret_cast<const float4*>(base + (int64_t)c * BS * 4);
+          const float4 qv = *reinterpret_cast<const float4*>(qs + 4 * c);
+          dot += qv.x * kv.x + qv.y * kv.y + qv.z * kv.z + qv.w * kv.w;
+        }
+      } else {
+        const float* row = kn + (start + key - ctx) * p.k_s0;
+        for (int c = 0; c < D / 4; ++c) {
+          const float4 kv = *reinterpret_cast<const float4*>(row + 4 * c);
+          const float4 qv = *reinterpret_cast<const float4*>(qs + 4 * c);
+          dot += qv.x * kv.x + qv.y * kv.y + qv.z * kv.z + qv.w * kv.w;
+        }
+      }
+      if (vis) logit = dot * scale + slope * (float)(key - pos_q);
+    }
+    float mx = logit;
+#pragma unroll
+    for (int sft = 16; sft >= 1; sft >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, sft));
+    const float m_new = fmaxf(m, mx);
+    if (m_new == kNegInf) continue;  // nothing visible yet (sliding window)
+    const float alpha = expf(m - m_new);
+    const float pr = vis ? expf(logit - m_new) : 0.f;
+    float ps = pr;
+#pragma unroll
+    for (int sft = 16; sft >= 1; sft >>= 1) ps += __shfl_xor_sync(0xffffffffu, ps, sft);
+    l = l * alpha + ps;
+    m = m_new;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) acc[u] *= alpha;
+    const int cnt = min(32, n - g0);
+    for (int jj = 0; jj < cnt; ++jj) {
+      const float pj = __shfl_sync(0xffffffffu, pr, jj);
+      const int64_t bj = __shfl_sync(0xffffffffu, blk, jj);
+      if (pj == 0.f) continue;  // warp-uniform
+      const int kj = g0 + jj;
+      if (kj < ctx) {
+        const float* vb = vc + bj * p.vc_bs + kj % BS;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int d = lane + 32 * u;
+          if (d < D) acc[u] += pj * vb[(int64_t)d * BS];
+        }
+      } else {
+        const float* vr = vn + (start + kj - ctx) * p.v_s0;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int d = lane + 32 * u;
+          if (d < D) acc[u] += pj * vr[d];
+        }
+      }
+    }
+  }
+  float* o = static_cast<float*>(p.out) + (start + i) * p.o_s0 + (int64_t)head * p.o_s1;
+  const float inv = l > 0.f ? 1.f / l : 0.f;
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int d = lane + 32 * u;
+    if (d < D) o[d] = acc[u] * inv;
+  }
+}
+
 namespace {
 
 template <int D, int BS>
@@ -478,15 +586,17 @@ extern "C" int b200_context_attention_fwd(
   if (num_seqs == 0 || max_query_len == 0) return B200_OK;
   B200_CHECK_ARG(num_kv_heads > 0 && num_heads % num_kv_heads == 0,
                  "num_heads (%d) must be a positive multiple of num_kv_heads (%d)", num_heads, num_kv_heads);
-  if (dtype != B200_DT_F16 && dtype != B200_DT_BF16) {
-    set_error("Unsupported data type: context_attention_fwd runs fp16 / bf16 (got %d)", dtype);
+  if (dtype != B200_DT_F16 && dtype != B200_DT_BF16 && dtype != B200_DT_F32) {
+    set_error("Unsupported data type: context_attention_fwd runs fp32 / fp16 / bf16 (got %d)", dtype);
     return B200_ERR_UNSUPPORTED;
   }
+  const int esz = dtype == B200_DT_F32 ? 4 : 2;
   auto a16 = [](const void* ptr) { return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0; };
-  B200_CHECK_ARG(a16(k) && a16(v) && a16(key_cache) && a16(value_cache) && k_stride0 % 8 == 0 &&
-                     k_stride1 % 8 == 0 && v_stride0 % 8 == 0 && v_stride1 % 8 == 0 &&
-                     kc_block_stride % 8 == 0 && kc_head_stride % 8 == 0 && vc_block_stride % 8 == 0 &&
-                     vc_head_stride % 8 == 0,
+  const int va = 16 / esz;  // elements per 16 bytes
+  B200_CHECK_ARG(a16(k) && a16(v) && a16(key_cache) && a16(value_cache) && k_stride0 % va == 0 &&
+                     k_stride1 % va == 0 && v_stride0 % va == 0 && v_stride1 % va == 0 &&
+                     kc_block_stride % va == 0 && kc_head_stride % va == 0 && vc_block_stride % va == 0 &&
+                     vc_head_stride % va == 0,
                  "context_attention_fwd: k/v/cache rows must be 16-byte aligned");
   B200_CHECK_ARG((reinterpret_cast<uintptr_t>(q) & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 3) == 0 &&
                      q_stride0 % 2 == 0 && q_stride1 % 2 == 0 && o_stride0 % 2 == 0 && o_stride1 % 2 == 0,
@@ -513,6 +623,18 @@ extern "C" int b200_context_attention_fwd(
                   (reinterpret_cast<uintptr_t>(kv_scratch) & 15) == 0)
                      ? static_cast<const unsigned char*>(kv_scratch)
                      : nullptr;
+  if (dtype == B200_DT_F32) {
+    B200_CHECK_ARG(head_size % 4 == 0 && head_size <= 256 && (reinterpret_cast<uintptr_t>(q) & 15) == 0 &&
+                       q_stride0 % 4 == 0 && q_stride1 % 4 == 0,
+                   "context_attention_fwd(fp32): head size must be a multiple of 4 (<= 256), q rows 16-byte aligned");
+    B200_CHECK_ARG(num_heads <= 65535 && num_seqs <= 65535, "context_attention_fwd: grid too large");
+    dim3 grid((max_query_len + 3) / 4, num_heads, num_seqs);
+    context_attention_f32_kernel<<<grid, 128, (size_t)4 * head_size * sizeof(float), (cudaStream_t)stream>>>(
+        p, head_size, block_size, scale);
+    count_launch();
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+  }
   if (dtype == B200_DT_F16)
     return dispatch_prefix<__half>(p, head_size, block_size, num_seqs, max_query_len, dev, (cudaStream_t)stream);
   return dispatch_prefix<__nv_bfloat16>(p, head_size, block_size, num_seqs, max_query_len, dev, (cudaStream_t)stream);
