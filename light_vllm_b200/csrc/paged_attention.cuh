@@ -245,7 +245,11 @@ __device__ __forceinline__ void process_page_ex(uint32_t k_smem, uint32_t v_smem
       for (int nt = 0; nt < NT; ++nt) mx = fmaxf(mx, fmaxf(s[nt][2 * rs], s[nt][2 * rs + 1]));
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-      const float m_new = fmaxf(m[rs], mx * scale_log2);
+      // Lazy reference point: m only has to keep exp2(x - m) in range, so it moves only when the
+      // step's maximum exceeds it by more than 2^8 (p <= 256 fits fp16/bf16; o and l are fp32);
+      // the accumulator rescale below then runs a handful of times per row instead of per new max.
+      const float m_cand = mx * scale_log2;
+      const float m_new = (m_cand > m[rs] + 8.f) ? m_cand : m[rs];
       alpha[rs] = fast_exp2(m[rs] - m_new);  // m_new is finite here: nothing is masked
       changed |= (m_new != m[rs]);
       m[rs] = m_new;
