@@ -238,7 +238,9 @@ int64_t b200_get_max_shared_memory_per_block_device_attribute(int64_t device_id)
  *     kv_scratch   optional device scratch of >= b200_context_attention_scratch_bytes(num_tokens =
  *                  rows of k/v, ...) bytes, 16-byte aligned: the new k/v are first rewritten into
  *                  page layout there (one extra launch) and then stream through the same bulk-copy
- *                  pipeline as the cached context; NULL (or too small) = each CTA stages them itself
+ *                  pipeline as the cached context; NULL (or too small) = each CTA stages them itself.
+ *                  The staged mode relies on start_loc being the packed prefix sums of the query
+ *                  lengths (non-decreasing in the sequence index), as query_start_loc[:-1] is.
  *   Query token i attends all ctx_len cached tokens and new tokens j <= i.
  */
 int b200_context_attention_fwd(
