@@ -187,7 +187,81 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
     const int smask = NS - 1, sshift = p.stage_shift;
     constexpr bool kPairOk = PLAIN && BS == 16;  // two pages per step on the unmasked fast path
     int i = 0, i_prev = 0, next_issue = min(NS, n_all);
+    if constexpr (kPairOk) {
+      // Interior of the context (full pages, no window, nothing masked): a tight loop over page
+      // pairs.  i stays even here and NS is even, so the pair's stages are adjacent (no wrap) and
+      // share one phase parity.
+      if (W == 0 && warp_on) {
+        const int n_fast = ctx / BS;  // full context pages (page0 == 0 without a window)
+        const int zi[RS] = {};
+        const float zf[RS] = {};
+        while (i + 2 <= n_fast) {
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {  // refill at most the two stages left one step ago
+            const int j = next_issue;
+            if (j < n_all && j - NS < i_prev) {
+              if (warp == (j & (kPrefixWarps - 1))) {
+                mbar_wait(empty_u32 + 8 * (j & smask), (uint32_t)(((j >> sshift) - 1) & 1));
+                issue(j, j & smask);
+              }
+              ++next_issue;
+            }
+          }
+          const int s = i & smask;
+          const uint32_t par = (uint32_t)((i >> sshift) & 1);
+          mbar_wait(full_u32 + 8 * s, par);
+          mbar_wait(full_u32 + 8 * s + 8, par);
+          const uint32_t ksm = ring_u32 + (uint32_t)s * STAGE_BYTES;
+          process_page_ex<T, D, BS, KV, GROWS, false, true, false, true, 2>(
+              ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, 2 * BS, p.scale_log2, slope, 0.f, row_on, zi, zi,
+              zf, (uint32_t)STAGE_BYTES);
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive(empty_u32 + 8 * s);
+            mbar_arrive(empty_u32 + 8 * s + 8);
+          }
+          i_prev = i;
+          i += 2;
+        }
+      }
+    }
     while (i < n_all) {
+      if constexpr (kPairOk) {
+        // Staged new-token slices entirely below this warp's causal frontier: same tight pair loop
+        // (i may be odd here, so the two stages can wrap and carry different parities).
+        if (W == 0 && warp_on && i >= n) {
+          const int zi[RS] = {};
+          const float zf[RS] = {};
+          while (i + 1 < n_all && (slice0 + i - n) * BS + 2 * BS - 1 <= w_tok_lo) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const int j = next_issue;
+              if (j < n_all && j - NS < i_prev) {
+                if (warp == (j & (kPrefixWarps - 1))) {
+                  mbar_wait(empty_u32 + 8 * (j & smask), (uint32_t)(((j >> sshift) - 1) & 1));
+                  issue(j, j & smask);
+                }
+                ++next_issue;
+              }
+            }
+            const int s = i & smask, s1 = (i + 1) & smask;
+            mbar_wait(full_u32 + 8 * s, (uint32_t)((i >> sshift) & 1));
+            mbar_wait(full_u32 + 8 * s1, (uint32_t)(((i + 1) >> sshift) & 1));
+            const uint32_t ksm = ring_u32 + (uint32_t)s * STAGE_BYTES;
+            process_page_ex<T, D, BS, KV, GROWS, false, true, false, true, 2>(
+                ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, 2 * BS, p.scale_log2, slope, 0.f, row_on, zi,
+                zi, zf, (uint32_t)(s1 - s) * (uint32_t)STAGE_BYTES);
+            __syncwarp();
+            if (lane == 0) {
+              mbar_arrive(empty_u32 + 8 * s);
+              mbar_arrive(empty_u32 + 8 * s1);
+            }
+            i_prev = i;
+            i += 2;
+          }
+          if (i >= n_all) break;
+        }
+      }
       // refill the stages every warp left at least one step ago (pages below i_prev)
       while (next_issue < n_all && next_issue - NS < i_prev) {
         const int j = next_issue++;
