@@ -225,6 +225,33 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
         }
       }
     }
+    if constexpr (PLAIN && BS == 32) {
+      // Same interior loop for 32-token pages: one page is already a full 32-token step.
+      if (W == 0 && warp_on) {
+        const int n_fast = ctx / BS;
+        const int zi[RS] = {};
+        const float zf[RS] = {};
+        while (i < n_fast) {
+          const int j = next_issue;
+          if (j < n_all && j - NS < i_prev) {
+            if (warp == (j & (kPrefixWarps - 1))) {
+              mbar_wait(empty_u32 + 8 * (j & smask), (uint32_t)(((j >> sshift) - 1) & 1));
+              issue(j, j & smask);
+            }
+            ++next_issue;
+          }
+          const int s = i & smask;
+          mbar_wait(full_u32 + 8 * s, (uint32_t)((i >> sshift) & 1));
+          const uint32_t ksm = ring_u32 + (uint32_t)s * STAGE_BYTES;
+          process_page_ex<T, D, BS, KV, GROWS, false, true, false, true>(
+              ksm, ksm + PAGE_BYTES, qa, o, m, l, lane, BS, p.scale_log2, slope, 0.f, row_on, zi, zi, zf);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(empty_u32 + 8 * s);
+          i_prev = i;
+          ++i;
+        }
+      }
+    }
     while (i < n_all) {
       if constexpr (kPairOk) {
         // Staged new-token slices entirely below this warp's causal frontier: same tight pair loop

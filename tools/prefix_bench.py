@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--heads", type=int, default=32)
     ap.add_argument("--kv-heads", type=int, default=8)
     ap.add_argument("--head-size", type=int, default=128)
+    ap.add_argument("--block-size", type=int, default=16)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--dtype", default="bfloat16")
@@ -39,7 +40,7 @@ def main():
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     dtype = getattr(torch, a.dtype)
-    B, ctx, ql, H, KH, D, BS = a.batch, a.ctx, a.qlen, a.heads, a.kv_heads, a.head_size, 16
+    B, ctx, ql, H, KH, D, BS = a.batch, a.ctx, a.qlen, a.heads, a.kv_heads, a.head_size, a.block_size
     T = B * ql
     g = torch.Generator(device=dev).manual_seed(3)
 
