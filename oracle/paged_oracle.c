@@ -462,7 +462,8 @@ int oracle_rotary_embedding(const int64_t* positions, void* query, void* key,
  * no mask :125-131) and the new tokens j <= i read from the packed k/v tensors (causal mask
  * :205-207).  sm_scale = 1/sqrt(D) (:702).  Sliding window: keys with pos_q - pos_k >= window get
  * the logit -10000 (:132-148, :208-211).  ALiBi: bias slope * (pos_k - pos_q), entries with a
- * positive bias are masked (:551-557, :622-628).  The Triton kernel runs the softmax online over
+ * positive bias are masked (:551-557, :622-628); the ALiBi kernel takes no window, so with slopes
+ * given the sliding window is ignored (:712-760).  The Triton kernel runs the softmax online over
  * 128-token tiles with fp32 statistics and rounds P to the value dtype before P.V (:170,:236);
  * this restatement computes the same softmax in one pass (fp32 logits, P rounded to T, fp32
  * accumulation) -- the tile order only changes fp32 summation order.
@@ -512,7 +513,7 @@ int oracle_context_attention_fwd(const void* q, const void* k, const void* v, vo
           }
           float s = dot * sm_scale;
           if (alibi_slopes) s += slope * (float)(t - pos_q);
-          if (sliding_window > 0 && pos_q - t >= sliding_window) s = -10000.f;
+          if (!alibi_slopes && sliding_window > 0 && pos_q - t >= sliding_window) s = -10000.f;
           logits[t] = s;
           mx = fmaxf(mx, s);
         }

@@ -144,6 +144,18 @@ def test_kernel_alibi(oracle):
 
 
 @pytest.mark.gpu
+def test_kernel_alibi_ignores_sliding_window(oracle):
+    """As the reference: _fwd_kernel_alibi has no SLIDING_WINDOW (prefix_prefill.py:712-760)."""
+    H = 4
+    slopes = torch.tensor([2.0 ** (-(j + 1) * 8.0 / H) for j in range(H)], dtype=torch.float32)
+    c = make_prefix_case([90, 3], [20, 40], H, 2, 64, 16, torch.float16, seed=31)
+    want = _call(oracle.context_attention_fwd, c, torch.zeros_like(c["query"]), slopes, 11)
+    assert (want.double() - ground_truth(c, slopes, 0)).abs().max().item() <= 2e-3
+    got = _gpu(c, slopes, 11)
+    assert (got.float() - want.float()).abs().max().item() <= 2e-3
+
+
+@pytest.mark.gpu
 def test_kernel_poisoned_cache_tail_and_spare_rows():
     """Cache slots past ctx_len (where the new tokens will be written) may hold anything."""
     c = make_prefix_case([21, 40], [30, 9], 8, 2, 128, 16, torch.float16, seed=2)
@@ -214,3 +226,79 @@ def test_kernel_fp32(oracle, H, KH, D, BS, window):
     got = _gpu(c, None, window)
     assert (got - want).abs().max().item() <= 2e-5
     assert (got.double() - ground_truth(c, None, window)).abs().max().item() <= 2e-5
+
+
+def _truth_gpu(c, slopes=None, window=0, dev="cuda:0"):
+    """ground_truth() vectorised per sequence in fp64 on the GPU (same definition; for larger cases)."""
+    q, k, v = (c[n].to(dev).double() for n in ("query", "key", "value"))
+    T, H, D = q.shape
+    KH, BS = c["num_kv_heads"], c["block_size"]
+    G = H // KH
+    kcache, vcache = c["key_cache"].to(dev), c["value_cache"].to(dev)
+    out = torch.zeros(T, H, D, dtype=torch.float64, device=dev)
+    for b in range(len(c["context_lens"])):
+        ctx = int(c["context_lens"][b])
+        ql = int(c["seq_lens"][b]) - ctx
+        if ql == 0:
+            continue
+        s0 = int(c["query_start_loc"][b])
+        nblk = (ctx + BS - 1) // BS
+        blks = c["block_tables"][b, :nblk].long().to(dev)
+        kc = kcache[blks].double().permute(1, 0, 3, 2, 4).reshape(KH, nblk * BS, D)[:, :ctx]
+        vc = vcache[blks].double().permute(1, 0, 3, 2).reshape(KH, nblk * BS, D)[:, :ctx]
+        keys = torch.cat([kc, k[s0:s0 + ql].transpose(0, 1)], dim=1)          # [KH, ctx+ql, D]
+        vals = torch.cat([vc, v[s0:s0 + ql].transpose(0, 1)], dim=1)
+        qq = q[s0:s0 + ql].view(ql, KH, G, D)
+        logits = torch.einsum("tkgd,ksd->kgts", qq, keys) * D ** -0.5           # [KH, G, ql, ctx+ql]
+        pos_k = torch.arange(ctx + ql, device=dev)
+        pos_q = ctx + torch.arange(ql, device=dev)
+        rel = (pos_k[None, :] - pos_q[:, None])                                 # [ql, S]
+        if slopes is not None:
+            logits = logits + slopes.to(dev).double().view(KH, G, 1, 1) * rel
+        mask = rel > 0
+        if window:
+            mask = mask | (-rel >= window)
+        logits = logits.masked_fill(mask, float("-inf"))
+        o = torch.einsum("kgts,ksd->tkgd", torch.softmax(logits, -1), vals)
+        out[s0:s0 + ql] = o.reshape(ql, H, D)
+    return out.cpu()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", range(40))
+def test_kernel_fuzz_against_fp64_truth(seed):
+    """Random shapes: group sizes that do not divide the row tile, odd page counts through the tight
+    interior loops, random windows / ALiBi, all three block sizes, with and without the staging pass."""
+    import random
+    r = random.Random(1000 + seed)
+    D = r.choice([64, 80, 96, 112, 120, 128, 192, 256])
+    BS = r.choice([8, 16, 16, 32])
+    G = r.choice([1, 2, 3, 4, 7, 8, 16])
+    KH = r.choice([1, 2, 3])
+    H = G * KH
+    dtype = r.choice([torch.float16, torch.bfloat16])
+    B = r.randint(1, 4)
+    ctx = [r.choice([0, r.randint(1, 40), r.randint(100, 1500)]) for _ in range(B)]
+    ql = [r.choice([1, r.randint(2, 40), r.randint(60, 260)]) for _ in range(B)]
+    window = r.choice([0, 0, r.randint(1, 50), r.randint(100, 900)])
+    slopes = None
+    if r.random() < 0.3:
+        slopes = torch.tensor([2.0 ** (-(j + 1) * 8.0 / H) for j in range(H)], dtype=torch.float32)
+    c = make_prefix_case(ctx, ql, H, KH, D, BS, dtype, seed=seed, q_pad=r.choice([0, 8]))
+    # the reference's ALiBi kernel takes no sliding window (prefix_prefill.py:712-760): window ignored
+    want = _truth_gpu(c, slopes, 0 if slopes is not None else window)
+    for use_scratch in (True, False):
+        got = _gpu(c, slopes, window, use_scratch=use_scratch)
+        assert torch.isfinite(got.float()).all()
+        err = (got.double() - want).abs().max().item()
+        assert err <= TOL[dtype], (seed, D, BS, G, KH, dtype, ctx, ql, window, slopes is not None,
+                                   use_scratch, err)
+
+
+def test_vectorised_truth_matches_loop_truth():
+    H = 6
+    slopes = torch.tensor([2.0 ** (-(j + 1) * 8.0 / H) for j in range(H)], dtype=torch.float32)
+    c = make_prefix_case([0, 21, 40], [9, 1, 17], H, 2, 64, 8, torch.float16, seed=77, q_pad=8)
+    for sl, w in [(None, 0), (slopes, 0), (None, 5), (slopes, 12)]:
+        a, b = ground_truth(c, sl, w), _truth_gpu(c, sl, w, dev="cpu")
+        assert (a - b).abs().max().item() <= 1e-7  # the loop version rounds the ALiBi bias to fp32
