@@ -295,3 +295,34 @@ def test_float32_vs_reference_cuda_kernels(ops, oracle):
         got, want = run(ops, g8, kv="fp8", ks=0.05, vs=0.03), run(rC, g8, kv="fp8", ks=0.05, vs=0.03)
         torch.cuda.synchronize()
         assert (got - want).abs().max().item() <= 1e-4
+
+
+@pytest.mark.parametrize("seed", range(32))
+def test_fuzz_against_fp64_truth(ops, seed):
+    """Random decode batches against the fp64 softmax: every head size / block size, group sizes the
+    row tile does not divide, batch sizes that flip the launch plan between clusters, splits and
+    plain CTAs, ragged lengths from 1 token to tens of thousands, ALiBi, strided queries; v1 and v2."""
+    import random
+    r = random.Random(5000 + seed)
+    D = r.choice(HEADS)
+    BS = r.choice([8, 16, 16, 32])
+    G = r.choice([1, 2, 3, 4, 5, 7, 8, 16])
+    KH = r.choice([1, 2, 4])
+    H = G * KH
+    dtype = r.choice([torch.float16, torch.bfloat16])
+    B = r.choice([1, 2, 3, 7, 19, 40])
+    longest = r.choice([40, 600, 3000, 20000 if B <= 3 else 3000])
+    lens = [r.choice([1, r.randint(1, 2 * BS), r.randint(1, longest)]) for _ in range(B)]
+    lens[r.randrange(B)] = longest
+    slopes = None
+    if r.random() < 0.3:
+        slopes = torch.tensor([2.0 ** (-(j + 1) * 8.0 / H) for j in range(H)], dtype=torch.float32)
+    c = make_case(B, H, KH, D, BS, lens, dtype, seed=seed, nan_padding=True, q_pad=r.choice([0, 8]))
+    want = naive_attention(c, alibi_slopes=slopes)
+    g = to_device(c, "cuda")
+    for run in (run_v1, run_v2):
+        got = run(ops, g, alibi=slopes.cuda() if slopes is not None else None)
+        torch.cuda.synchronize()
+        err = (got.double().cpu() - want).abs().max().item()
+        assert err <= TOL[dtype], (seed, run.__name__, D, BS, G, KH, dtype, B, longest,
+                                   slopes is not None, err)
