@@ -326,3 +326,25 @@ def test_fuzz_against_fp64_truth(ops, seed):
         err = (got.double().cpu() - want).abs().max().item()
         assert err <= TOL[dtype], (seed, run.__name__, D, BS, G, KH, dtype, B, longest,
                                    slopes is not None, err)
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_fuzz_fp8_against_oracle(ops, oracle, seed):
+    """Random decode batches over fp8 (e4m3 / e5m2) caches with random scales, v1 and v2, against the
+    oracle (whose fp8 codec is pinned bit-exact on the reference's tables)."""
+    import random
+    r = random.Random(7000 + seed)
+    D = r.choice([64, 80, 96, 112, 128, 192, 256])
+    BS = r.choice([8, 16, 16, 32])
+    G = r.choice([1, 2, 3, 4, 7, 8, 16])
+    KH = r.choice([1, 2, 4])
+    dtype = r.choice([torch.float16, torch.bfloat16])
+    kv = r.choice(["fp8", "fp8_e5m2"])
+    B = r.choice([1, 2, 5, 19, 40])
+    longest = r.choice([40, 600, 3000, 12000 if B <= 2 else 3000])
+    lens = [r.choice([1, r.randint(1, 2 * BS), r.randint(1, longest)]) for _ in range(B)]
+    lens[r.randrange(B)] = longest
+    ks, vs = r.choice([1.0, 0.05, 0.3]), r.choice([1.0, 0.02, 2.0])
+    c = make_fp8_case(oracle, lens, G * KH, KH, D, BS, dtype, kv, ks, vs, seed=seed)
+    for version in (1, 2):
+        check(ops, oracle, c, dtype, version, kv=kv, ks=ks, vs=vs)
