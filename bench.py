@@ -12,7 +12,8 @@ batch 64, ctx 2048, paged_attention_v1.
 Printed JSON (one line, rank 0):
   value      KV bytes read per second, whole job, inputs resident in HBM (device timed, max over ranks)
   e2e        same metric through the attention plugin with HOST (pinned) inputs: per step the
-             H2D copy of q/k/v + metadata and the D2H read of the output are inside the timed region
+             H2D copy of q/k/v + metadata and the D2H read of the output are inside the timed region;
+             the step is replayed as one CUDA graph (e2e.eager_* = the same step enqueued from Python)
   roofline   the attention kernel alone: algorithmic bytes per launch / CUDA-event launch time
   cpu_baseline  the reference's own CPU kernels (oracle/_ref/libref_cpu.so) or the C oracle port,
              timed on this box's host cores on a bounded sample
@@ -341,7 +342,7 @@ def run_b200_arm(args, c):
     # ---- the same step through the plugin, from HOST buffers ----
     impl = PagedB200AttentionBackend.get_impl_cls()(H, D, scale, KH, None, None, kv)
 
-    def e2e_step():
+    def e2e_body():
         x = qkv_h.to(dev, non_blocking=True)
         meta = PagedB200AttentionMetadata(
             num_prefills=0, num_prefill_tokens=0, num_decode_tokens=B, slot_mapping=slots_h,
@@ -354,6 +355,9 @@ def run_b200_arm(args, c):
         for l in range(L):
             o = impl.forward(xq, xk, xv, pools[l], meta, k_scale, v_scale)
         out_h.copy_(o, non_blocking=True)
+
+    def e2e_step():  # eager: every copy and launch enqueued from Python
+        e2e_body()
         torch.cuda.current_stream().synchronize()
 
     h2d = qkv_h.numel() * qkv_h.element_size() + slots_h.numel() * 8 + seq_lens_h.numel() * 4 + \
@@ -405,13 +409,39 @@ def run_b200_arm(args, c):
     ms_attn = timed(attn_only, reps) / reps
     for _ in range(max(args.warmup, 3)):
         e2e_step()
-    ms_e2e = timed(e2e_step, args.steps)
+    ms_e2e_eager = timed(e2e_step, args.steps)
+    out_eager = out_h.clone()
+
+    # The same step (pinned-host H2D copies, L plugin forwards, D2H read of the result) captured
+    # once in a CUDA graph and replayed per step, the way a decode engine runs a fixed-shape decode
+    # step: the host refreshes the pinned buffers, launches ONE graph and waits for the result.
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        e2e_body()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        e2e_body()
+
+    def e2e_graph_step():
+        graph.replay()
+        torch.cuda.current_stream().synchronize()
+
+    out_h.zero_()
+    for _ in range(max(args.warmup, 3)):
+        e2e_graph_step()
+    if not torch.equal(out_h, out_eager):
+        raise RuntimeError("graph-replayed e2e step disagrees with the eager e2e step")
+    ms_e2e = timed(e2e_graph_step, args.steps)
 
     pre = None
     if preempt:
         pre = preemption_exercise(args, c, dev, pools, block_tables_h, NB, device_step, timed)
 
-    return dict(rank=rank, world=world, ms_total=ms_total, ms_e2e=ms_e2e, ms_attn=ms_attn,
+    return dict(rank=rank, world=world, ms_total=ms_total, ms_e2e=ms_e2e, ms_e2e_eager=ms_e2e_eager,
+                ms_attn=ms_attn,
                 clocks=clocks, launches=launches, h2d=h2d, d2h=d2h, L=L, preemption=pre,
                 plan=_lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, local_rank),
                 dist=dist if world > 1 else None)
@@ -567,7 +597,11 @@ def main():
             "e2e": {"value": round(e2e, 1), "unit": "GB/s", "h2d_bytes_per_step": r["h2d"],
                     "d2h_bytes_per_step": r["d2h"], "ms_per_step": round(e2e_s * 1e3, 4),
                     "api": "PagedB200AttentionImpl.forward per layer pool, pinned host q/k/v + "
-                           "metadata in, output read back"},
+                           "metadata in, output read back; the step (H2D copies, forwards, D2H "
+                           "read) is captured once in a CUDA graph and replayed + synchronised "
+                           "per step",
+                    "eager_ms_per_step": round(r["ms_e2e_eager"] / args.steps, 4),
+                    "eager_value": round(world * L * kvb / (r["ms_e2e_eager"] / 1e3 / args.steps) / 1e9, 1)},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
                          "unit": "GB/s", "frac": round(achieved / peak, 4),
                          "traffic": None if (args.ctx or args.batch) else ncu_traffic(args.config),
