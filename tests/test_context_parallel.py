@@ -187,6 +187,36 @@ def test_virtual_ranks_match_oracle(oracle, dtype, tol, world, chunk):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("seed", range(12))
+def test_virtual_ranks_fuzz_against_fp64_truth(seed):
+    """Random worlds / chunk sizes / head shapes / ragged lengths (many sequences own no block on
+    some rank): every rank's merged output against the fp64 softmax over the whole context."""
+    import random
+    r = random.Random(9000 + seed)
+    world = r.choice([2, 3, 4, 8])
+    chunk = r.choice([1, 2, 4])
+    D = r.choice([64, 80, 96, 112, 120, 128, 192, 256])
+    BS = r.choice([8, 16, 16, 32])
+    G = r.choice([1, 2, 4, 7, 8])
+    KH = r.choice([1, 2, 4])
+    dtype = r.choice([torch.float16, torch.bfloat16])
+    B = r.choice([1, 2, 5, 9])
+    longest = r.choice([60, 900, 4000, 9000])
+    lens = [r.choice([0, 1, r.randint(1, 3 * BS), r.randint(1, longest)]) for _ in range(B)]
+    lens[r.randrange(B)] = longest
+    case = make_case(B, G * KH, KH, D, BS, lens, dtype, seed=seed, nan_padding=True)
+    want = naive_attention(case)
+    outs = _run_virtual(case, world, chunk, calls=2)
+    live = torch.tensor(lens) > 0
+    tol = 2e-3 if dtype == torch.float16 else 1e-2
+    for rank, o in enumerate(outs):
+        err = (o.double()[live] - want[live]).abs().max().item()
+        assert err <= tol, (seed, rank, world, chunk, D, BS, G, KH, dtype, lens, err)
+    for o in outs[1:]:
+        assert torch.equal(o[live], outs[0][live])
+
+
+@pytest.mark.gpu
 def test_virtual_ranks_fp8_and_small_heads(oracle):
     lens = [40, 1300, 513]
     case = make_case(len(lens), 28, 4, 128, 16, lens, torch.bfloat16, seed=3)
