@@ -182,3 +182,32 @@ def test_vs_reference_cuda_cache_kernels(ops):
     ops.convert_fp8(d1, q1, 0.07, "fp8")
     rcache.convert_fp8(d2, q1, 0.07, "fp8")
     assert torch.equal(raw(d1), raw(d2))
+
+
+@pytest.mark.parametrize("seed", range(20))
+def test_reshape_and_cache_fuzz_bit_exact(ops, oracle, seed):
+    """Random token counts (1 .. thousands), head counts / sizes, block sizes, row paddings, dtypes
+    and fp8 scales: cache bytes identical to the oracle's, untouched slots included."""
+    import random
+    r = random.Random(3000 + seed)
+    dtype, kv, ks, vs = r.choice(CASES)
+    cache_dtype = dtype if kv == "auto" else torch.uint8
+    x = elem_x(cache_dtype)
+    D = r.choice([d for d in (64, 80, 96, 112, 120, 128, 192, 256) if d % x == 0])
+    KH = r.choice([1, 2, 3, 8])
+    BS = r.choice([8, 16, 32])
+    T = r.choice([1, 2, r.randint(3, 100), r.randint(500, 3000)])
+    NB = (T + BS - 1) // BS + r.randint(1, 5)
+    pad = r.choice([0, 8, 64])
+    key, value, kc, vc, slots = make_kv_inputs(T, KH, D, BS, NB, dtype, cache_dtype, seed=seed,
+                                               stride_pad=pad)
+    kc_o, vc_o = kc.clone(), vc.clone()
+    oracle.reshape_and_cache(key, value, kc_o, vc_o, slots, kv, ks, vs)
+    kc_g, vc_g = kc.cuda(), vc.cuda()
+    kg = torch.empty(T, KH * D + pad, dtype=dtype, device="cuda")[:, :KH * D].view(T, KH, D)
+    vg = torch.empty(T, KH * D + pad, dtype=dtype, device="cuda")[:, :KH * D].view(T, KH, D)
+    kg.copy_(key)
+    vg.copy_(value)
+    ops.reshape_and_cache(kg, vg, kc_g, vc_g, slots.cuda(), kv, ks, vs)
+    assert torch.equal(raw(kc_g), raw(kc_o)), (seed, dtype, kv, D, KH, BS, T)
+    assert torch.equal(raw(vc_g), raw(vc_o)), (seed, dtype, kv, D, KH, BS, T)
