@@ -191,3 +191,38 @@ def test_fused_rope_cache_write_equals_two_ops(ops, dtype, kv, ks, vs, is_neox):
             res.append((a, kc, vc))
         for u, w in zip(*res):
             assert torch.equal(bits(u), bits(w)), (T, H, KH, D, BS, rot)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", range(16))
+def test_rope_fuzz_bit_exact(ops, oracle, seed):
+    """Random token counts, head counts (GQA), head sizes, partial rotary dims, both styles, all
+    dtypes, with and without per-token cache offsets: output bits == the oracle's."""
+    import random
+    r = random.Random(11000 + seed)
+    dtype = r.choice([torch.float16, torch.bfloat16, torch.float32])
+    D = r.choice([64, 80, 96, 128, 256])
+    rot = r.choice([D, D // 2])
+    H = r.choice([1, 4, 14, 32])
+    KH = r.choice([k for k in (1, 2, 4, 14, 32) if k <= H and H % k == 0])
+    T = r.choice([1, 3, r.randint(4, 200), r.randint(1000, 4000)])
+    neox = r.random() < 0.5
+    max_pos = 4096
+    g = torch.Generator().manual_seed(seed)
+    q = (torch.rand(T, H * D, generator=g) * 2 - 1).to(dtype)
+    k = (torch.rand(T, KH * D, generator=g) * 2 - 1).to(dtype)
+    batched = r.random() < 0.4
+    n_caches = 3 if batched else 1
+    cache = torch.cat([cos_sin_cache(max_pos, rot, dtype, base=10000.0 * (i + 1)) for i in range(n_caches)])
+    pos = torch.randint(0, max_pos, (T,), generator=g, dtype=torch.int64)
+    offs = (torch.randint(0, n_caches, (T,), generator=g, dtype=torch.int64) * max_pos) if batched else None
+    qo, ko = q.clone(), k.clone()
+    oracle.rotary_embedding(pos, qo, ko, D, cache, neox, rot, offs)
+    qg, kg = q.cuda(), k.cuda()
+    if batched:
+        ops.batched_rotary_embedding(pos.cuda(), qg, kg, D, cache.cuda(), neox, rot, offs.cuda())
+    else:
+        ops.rotary_embedding(pos.cuda(), qg, kg, D, cache.cuda(), neox)
+    info = (seed, dtype, D, rot, H, KH, T, neox, batched)
+    assert torch.equal(bits(qg.cpu()), bits(qo)), info
+    assert torch.equal(bits(kg.cpu()), bits(ko)), info
