@@ -348,3 +348,32 @@ def test_fuzz_fp8_against_oracle(ops, oracle, seed):
     c = make_fp8_case(oracle, lens, G * KH, KH, D, BS, dtype, kv, ks, vs, seed=seed)
     for version in (1, 2):
         check(ops, oracle, c, dtype, version, kv=kv, ks=ks, vs=vs)
+
+
+@pytest.mark.parametrize("version", [1, 2])
+@pytest.mark.parametrize("H,KH,D,BS", [(32, 8, 128, 16), (7, 1, 80, 8), (16, 1, 256, 32)])
+def test_writes_only_its_output_rows(ops, version, H, KH, D, BS):
+    """Guard rows around the output keep their sentinel and the inputs (query, caches, block tables,
+    lengths) are bit-identical after the call; zero-length sequences' rows are not required to be
+    written and everything else matches the fp64 truth."""
+    lens = [1, 0, 3 * BS, 700, 2300]
+    c = make_case(len(lens), H, KH, D, BS, lens, torch.float16, seed=77, nan_padding=True)
+    g = to_device(c, "cuda")
+    B = len(lens)
+    big = torch.full((B + 4, H, D), 777.0, dtype=torch.float16, device="cuda")
+    out = big[2:-2]
+    before = {n: g[n].clone() for n in ("query", "key_cache", "value_cache", "block_tables", "seq_lens")}
+    if version == 1:
+        ops.paged_attention_v1(out, *attn_args(g))
+    else:
+        es, ml, tmp = v2_scratch(c, device="cuda")
+        ops.paged_attention_v2(out, es, ml, tmp, *attn_args(g))
+    torch.cuda.synchronize()
+    assert (big[:2] == 777.0).all() and (big[-2:] == 777.0).all()
+    for n, t in before.items():
+        same = torch.equal(t, g[n]) if t.dtype in (torch.int32, torch.int64) else \
+            torch.equal(t.view(torch.uint8), g[n].view(torch.uint8))
+        assert same, n
+    live = torch.tensor(lens) > 0
+    want = naive_attention(c)
+    assert (out.double().cpu()[live] - want[live]).abs().max().item() <= 2e-3

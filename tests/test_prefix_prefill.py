@@ -302,3 +302,25 @@ def test_vectorised_truth_matches_loop_truth():
     for sl, w in [(None, 0), (slopes, 0), (None, 5), (slopes, 12)]:
         a, b = ground_truth(c, sl, w), _truth_gpu(c, sl, w, dev="cpu")
         assert (a - b).abs().max().item() <= 1e-7  # the loop version rounds the ALiBi bias to fp32
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,KH,D,BS", [(32, 8, 128, 16), (7, 1, 80, 8), (4, 2, 256, 32)])
+def test_kernel_writes_only_its_output_rows(H, KH, D, BS):
+    """Guard rows and guard columns around a strided output keep their sentinel; q/k/v, the caches
+    and the block tables are bit-identical after the call (the staging pass writes only scratch)."""
+    from light_vllm_b200.attention.prefix_prefill import context_attention_fwd
+    c = make_prefix_case([0, 37, 300], [45, 1, 70], H, KH, D, BS, torch.float16, seed=41, q_pad=8)
+    d = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in c.items()}
+    T = d["query"].shape[0]
+    big = torch.full((T + 4, H * D + 24), 777.0, dtype=torch.float16, device="cuda")
+    out = big[2:-2, 8:8 + H * D].view(T, H, D)
+    before = {n: d[n].clone() for n in ("query", "key", "value", "key_cache", "value_cache", "block_tables")}
+    _call(context_attention_fwd, d, out)
+    torch.cuda.synchronize()
+    assert (big[:2] == 777.0).all() and (big[-2:] == 777.0).all()
+    assert (big[:, :8] == 777.0).all() and (big[:, 8 + H * D:] == 777.0).all()
+    for n, t in before.items():
+        assert torch.equal(t.view(torch.uint8) if t.dtype != torch.int32 else t,
+                           d[n].view(torch.uint8) if t.dtype != torch.int32 else d[n]), n
+    assert (out.double().cpu() - ground_truth(c)).abs().max().item() <= 2e-3
