@@ -261,6 +261,154 @@ def run_reference_arm(args, c):
     print(json.dumps(line), flush=True)
 
 
+
+# --------------------------------------------------------------------------------------------
+# Checker legs (untimed region; the only other places bench.py touches oracle/): the step's output
+# against the CPU oracle on a slice of the batch, and the reference's own CUDA kernels
+# (oracle/_ref/libref_cuda.so, recompiled for sm_100a) timed on the same pools -- SURVEY 0.3 / 8d's bar.
+# --------------------------------------------------------------------------------------------
+def oracle_slice_check(c, q, out, kc, vc, block_tables, seq_lens, scale, k_scale, v_scale):
+    """max-abs of the product's `out` rows vs oracle/paged_oracle.c on up to 4 sequences of the
+    batch (their pages gathered out of the pool and renumbered); asserts BASELINE.json's budget."""
+    import torch
+    from oracle import oracle
+    B, BS, KH, ctx = c["B"], c["BS"], c["KH"], c["ctx"]
+    per_seq = ctx * KH * c["D"] * 2 * kc.element_size()
+    n = max(1, min(4, B, (1 << 30) // max(per_seq, 1)))
+    rows = sorted({0, B // 3, (2 * B) // 3, B - 1})[:n]
+    bps = (ctx + BS - 1) // BS
+    blks = block_tables[rows].long().reshape(-1)
+    case_kc, case_vc = kc[blks].cpu().contiguous(), vc[blks].cpu().contiguous()
+    bt = torch.arange(len(rows) * bps, dtype=torch.int32).view(len(rows), bps)
+    qs = q[rows].cpu().contiguous()
+    want = torch.empty_like(qs)
+    lens = seq_lens[rows].cpu()
+    tail = (qs, case_kc, case_vc, KH, scale, bt, lens, BS, ctx, None, c["kv"], k_scale, v_scale)
+    if c["version"] == 1:
+        oracle.paged_attention_v1(want, *tail)
+    else:
+        H, D = qs.shape[1], qs.shape[2]
+        P = (ctx + 511) // 512
+        es = torch.empty(len(rows), H, P, dtype=torch.float32)
+        oracle.paged_attention_v2(want, es, torch.empty_like(es),
+                                  torch.empty(len(rows), H, P, D, dtype=qs.dtype), *tail)
+    err = (out[rows].float().cpu() - want.float()).abs().max().item()
+    tol = 2e-3 if c["dtype"] == "float16" else 1e-2
+    if not err <= tol:
+        raise RuntimeError(f"bench step output differs from the oracle: max-abs {err} > {tol}")
+    return {"max_abs": err, "tol": tol, "sequences": rows, "against": "oracle/paged_oracle.c (CPU)"}
+
+
+def reference_cuda_leg(c, timed, run_attention_with, L, reps, ms_attn):
+    """Times torch.ops._ref_C.paged_attention_v1/v2 -- the reference's attention_kernels.cu built for
+    sm_100a by oracle/Makefile -- with the product's own CUDA-event loop, pools and block tables."""
+    from oracle import ref
+    if not ref.have_ref_cuda():
+        return {"unavailable": "oracle/_ref/libref_cuda.so not built"}
+    rC, _ = ref.ref_cuda()
+    for l in range(L):
+        run_attention_with(rC, l)
+    counter = [0]
+
+    def one():
+        run_attention_with(rC, counter[0] % L)
+        counter[0] += 1
+
+    ms = timed(one, reps) / reps
+    return {"us_per_launch": round(ms * 1e3, 2),
+            "GBps": round(algorithmic_bytes_attention(c) / (ms / 1e3) / 1e9, 1),
+            "speedup": round(ms / ms_attn, 3),
+            "kernel": f"reference paged_attention_v{c['version']} (csrc/attention/attention_kernels.cu "
+                      f"recompiled for sm_100a), {reps} launches, same pools / block tables / events"}
+
+
+def ctx_shard_record(dev, rank, world, dist, steps):
+    """--gpus N >= 2, after the timed region: ONE sequence batch's context split over the N ranks
+    (real one-process-per-GPU ranks over CUDA IPC, NVLink peer stores inside the merge kernel; no
+    NCCL on the data path) vs the same decode step on one GPU (paged_attention_v2).  Strong scaling;
+    device-timed, max over ranks.  4 x 128 Ki tokens and 1 x 128 Ki tokens, Llama-3-8B-shaped bf16."""
+    import torch
+    from light_vllm_b200 import _custom_ops as ops
+    from light_vllm_b200.context_parallel import ContextShardGroup, ContextSharding
+    H, KH, D, BS, ctx, layers = 32, 8, 128, 16, 131072, 2
+    dtype = torch.bfloat16
+    scale = D ** -0.5
+    rec = {}
+    for B in (4, 1):
+        nblk = ctx // BS
+        NB = B * nblk + 8
+        g = torch.Generator(device=dev).manual_seed(1234)   # same pool on every rank
+        pools = []
+        for _ in range(layers):
+            kc = torch.empty(NB, KH, D // 8, BS, 8, device=dev, dtype=dtype).uniform_(-0.5, 0.5, generator=g)
+            vc = torch.empty(NB, KH, D, BS, device=dev, dtype=dtype).uniform_(-0.5, 0.5, generator=g)
+            pools.append((kc, vc))
+        q = torch.empty(B, H, D, device=dev, dtype=dtype).uniform_(-0.25, 0.25, generator=g)
+        perm = torch.randperm(NB, generator=torch.Generator().manual_seed(7))[:B * nblk].int().view(B, nblk)
+        lens = [ctx] * B
+        bt_full = perm.to(dev)
+        sl_full = torch.tensor(lens, dtype=torch.int32, device=dev)
+        P = ctx // 512
+        es = torch.empty(B, H, P, dtype=torch.float32, device=dev)
+        ml = torch.empty_like(es)
+        tmp = torch.empty(B, H, P, D, dtype=dtype, device=dev)
+        out_ref, out = torch.empty_like(q), torch.empty_like(q)
+
+        def base_step(i):
+            kc, vc = pools[i % layers]
+            ops.paged_attention_v2(out_ref, es, ml, tmp, q, kc, vc, KH, scale, bt_full, sl_full, BS,
+                                   ctx, None, "auto", 1.0, 1.0)
+
+        sh = ContextSharding(world, BS, 4)
+        grp = ContextShardGroup.create(B * H, D, dev.index)
+        bt, ll, mx = sh.shard_batch(perm, lens, rank)
+        bt, ll = bt.to(dev), ll.to(dev)
+
+        def shard_step(i):
+            kc, vc = pools[i % layers]
+            grp.paged_attention(out, q, kc, vc, KH, scale, bt, ll, BS, mx)
+
+        def timed(fn):
+            for i in range(5):
+                fn(i)
+            torch.cuda.synchronize()
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(steps):
+                fn(i)
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return t.item()
+
+        base_ms = timed(base_step)
+        shard_ms = timed(shard_step)
+        base_step(0)
+        shard_step(0)
+        torch.cuda.synchronize()
+        st = torch.tensor([float(grp.status()), (out.float() - out_ref.float()).abs().max().item()],
+                          device=dev)
+        dist.all_reduce(st, op=dist.ReduceOp.MAX)
+        kv_bytes = B * ctx * KH * D * 2 * 2
+        rec[f"{B}x{ctx}"] = {
+            "ms": round(shard_ms, 4), "single_gpu_ms": round(base_ms, 4),
+            "speedup": round(base_ms / shard_ms, 3), "max_abs": st[1].item(),
+            "exchange_status": int(st[0].item()),
+            "aggregate_kv_GBps": round(kv_bytes / shard_ms / 1e6, 1)}
+        if not st[1].item() <= 1e-2 or st[0].item() != 0:
+            raise RuntimeError(f"context-sharded decode disagrees with the single-GPU result: {rec}")
+        grp.close()
+        del pools, es, ml, tmp
+        torch.cuda.empty_cache()
+    rec["note"] = (f"one decode step, bf16 H{H}/KH{KH}/D{D}/BS{BS}, pages dealt round-robin (4-page "
+                   f"chunks) to {world} one-process-per-GPU ranks; CUDA-IPC exchange buffers, peer "
+                   "stores + epoch flags inside the merge kernel; strong scaling vs the whole context "
+                   "on ONE GPU (paged_attention_v2); device-timed, max over ranks; max_abs vs that result")
+    return rec
+
 # --------------------------------------------------------------------------------------------
 # B200 arm
 # --------------------------------------------------------------------------------------------
@@ -325,14 +473,17 @@ def run_b200_arm(args, c):
                torch.empty(B, H, P, dtype=torch.float32, device=dev),
                torch.empty(B, H, P, D, dtype=dtype, device=dev))
 
-    def attention(l):
+    def attention_with(mod, l):
         kc, vc = split[l]
         if c["version"] == 1:
-            ops.paged_attention_v1(out, q, kc, vc, KH, scale, block_tables, seq_lens, BS, ctx, None,
-                                   kv, k_scale, v_scale)
+            mod.paged_attention_v1(out, q, kc, vc, KH, scale, block_tables, seq_lens, BS, ctx, None,
+                                   kv, k_scale, v_scale, 0, 0, 0, 64, 0)
         else:
-            ops.paged_attention_v2(out, *scratch, q, kc, vc, KH, scale, block_tables, seq_lens, BS,
-                                   ctx, None, kv, k_scale, v_scale)
+            mod.paged_attention_v2(out, *scratch, q, kc, vc, KH, scale, block_tables, seq_lens, BS,
+                                   ctx, None, kv, k_scale, v_scale, 0, 0, 0, 64, 0)
+
+    def attention(l):
+        attention_with(ops, l)
 
     def device_step():
         for l in range(L):
@@ -408,6 +559,18 @@ def run_b200_arm(args, c):
         counter[0] += 1
 
     ms_attn = timed(attn_only, reps) / reps
+
+    # ---- checker legs (untimed): oracle on a slice of the step's output, reference CUDA kernels ----
+    device_step()
+    torch.cuda.synchronize()
+    parity = None
+    if rank == 0:
+        kc_l, vc_l = split[L - 1]
+        parity = oracle_slice_check(c, q, out, kc_l, vc_l, block_tables, seq_lens, scale, k_scale,
+                                    v_scale)
+    ref_cuda = None
+    if not args.no_reference_cuda:
+        ref_cuda = reference_cuda_leg(c, timed, attention_with, L, max(5, min(reps, 10)), ms_attn)
     for _ in range(max(args.warmup, 3)):
         e2e_step()
     ms_e2e_eager = timed(e2e_step, args.steps)
@@ -441,8 +604,14 @@ def run_b200_arm(args, c):
     if preempt:
         pre = preemption_exercise(args, c, dev, pools, block_tables_h, NB, device_step, timed)
 
+    ctx_shard = None
+    if world > 1 and not args.no_ctx_shard:
+        del pools, split, graph
+        torch.cuda.empty_cache()
+        ctx_shard = ctx_shard_record(dev, rank, world, dist, max(10, args.steps))
+
     return dict(rank=rank, world=world, ms_total=ms_total, ms_e2e=ms_e2e, ms_e2e_eager=ms_e2e_eager,
-                ms_attn=ms_attn,
+                ms_attn=ms_attn, parity=parity, reference_cuda=ref_cuda, ctx_shard=ctx_shard,
                 clocks=clocks, launches=launches, h2d=h2d, d2h=d2h, L=L, preemption=pre,
                 plan=_lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, local_rank),
                 dist=dist if world > 1 else None)
@@ -553,6 +722,10 @@ def main():
     ap.add_argument("--preempt-every", type=int, default=8,
                     help="c5: decode steps between preemption cycles in the mixed measurement")
     ap.add_argument("--no-preempt", action="store_true", help="c5: skip the preemption exercise")
+    ap.add_argument("--no-reference-cuda", action="store_true",
+                    help="skip the (untimed-region) leg that times the reference's CUDA kernels")
+    ap.add_argument("--no-ctx-shard", action="store_true",
+                    help="--gpus N >= 2: skip the context-sharded decode record")
     args = ap.parse_args()
     c = dict(CONFIGS[args.config])
     if args.ctx:
@@ -570,7 +743,7 @@ def main():
     cpu = None
     if r["rank"] == 0 and world == 1 and args.cpu_budget > 0:
         try:
-            cpu = time_cpu(c, budget_s=args.cpu_budget)
+            cpu = time_cpu(c, budget_s=args.cpu_budget, warmup=3)
         except Exception as e:  # the baseline is reported, never required for the GPU numbers
             cpu = {"error": repr(e)}
     if r["rank"] == 0:
@@ -614,14 +787,21 @@ def main():
         }
         if r.get("preemption") is not None:
             line["preemption"] = r["preemption"]
+        if r.get("parity") is not None:
+            line["parity"] = r["parity"]
+        if r.get("reference_cuda") is not None:
+            line["reference_cuda"] = r["reference_cuda"]
+        if r.get("ctx_shard") is not None:
+            line["ctx_shard"] = r["ctx_shard"]
         if cpu is not None and "error" not in cpu:
-            gbs = cpu["kv_bytes"] / cpu["best_s"] / 1e9
+            # same statistic as the --impl reference arm: MEAN over the timed steps (>= 3 untimed)
+            gbs = cpu["kv_bytes"] / cpu["mean_s"] / 1e9
             line["cpu_baseline"] = {
                 "value": round(gbs, 3), "unit": "GB/s", "cores": cpu["cores"], "kind": cpu["kind"],
                 "sample": f"{cpu['sample_B']} of {c['B']} sequences x ctx {c['ctx']}, 1 layer pool, "
                           f"{cpu['dtype']} (CPU path has no fp16/fp8), reshape_and_cache + "
-                          f"paged_attention_v{c['version']}, best of {cpu['n']} "
-                          f"({cpu['best_s'] * 1e3:.1f} ms)"}
+                          f"paged_attention_v{c['version']}, mean of {cpu['n']} steps after 3 untimed "
+                          f"({cpu['mean_s'] * 1e3:.1f} ms/step; best {cpu['best_s'] * 1e3:.1f} ms)"}
         elif cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)

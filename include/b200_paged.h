@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define B200_PAGED_ABI_VERSION 1
+#define B200_PAGED_ABI_VERSION 2
 
 typedef struct CUstream_st* b200_stream_t; /* == cudaStream_t */
 
@@ -290,6 +290,16 @@ int b200_paged_attention_ctx_shard(
     float v_scale, int q_dtype, int kv_dtype, void* const* exchange_bufs, int rank, int world,
     int max_pairs, uint32_t epoch, int phases, int device, b200_stream_t stream);
 int b200_ctx_exchange_status(const void* local_buf, int world, int32_t* status, int device);
+/* A wait that times out is LOUD: the waiting rank's output rows of that call are NaN, status word 0
+ * holds 1 + the rank that never published and word 3 the epoch of the failing call (sticky until
+ * b200_ctx_exchange_clear_status).  b200_ctx_exchange_status_async copies the 4 status words into
+ * pinned host memory on `stream`, so that the host can check call n when it issues call n+1 without
+ * synchronising; b200_ctx_exchange_set_timeout sets this group's timeout (ms, 0 = 2000 ms default).
+ * All state lives in the group's own exchange buffer. */
+int b200_ctx_exchange_status_async(const void* local_buf, int world, int32_t* pinned_host4, int device,
+                                   b200_stream_t stream);
+int b200_ctx_exchange_set_timeout(void* local_buf, int world, int timeout_ms, int device);
+int b200_ctx_exchange_clear_status(void* local_buf, int world, int device);
 
 /* Peer-visible device memory for the exchange buffers: plain cudaMalloc (zero-filled) exported /
  * opened through CUDA IPC handles (64 bytes) that the host side passes between the ranks. */
@@ -308,16 +318,38 @@ typedef struct {
   int32_t ctas_per_sm;    /* occupancy reported by the runtime                    */
   int32_t grid_x, grid_y, grid_z;
 } b200_attn_plan_t;
+/* Per-call launch overrides for benchmarking / autotuning (every field: 0 = library default).  The
+ * library keeps NO mutable state between calls and reads no environment variables (the reference's
+ * ops are stateless, and DP replicas call them from one thread per GPU,
+ * prefill_only/executor/gpu_data_parallelism_executor.py:41-72): overrides travel as arguments. */
+typedef struct {
+  int32_t num_warps;   /* warps per CTA (1..8)                                              */
+  int32_t num_stages;  /* K+V page pairs in flight per warp                                 */
+  int32_t split;       /* v1: cluster size (context split through DSMEM); v2: partition     */
+                       /* length in units of 512 tokens                                     */
+} b200_attn_tuning_t;
 int b200_paged_attention_plan(int version, int num_seqs, int num_heads, int num_kv_heads,
                               int head_size, int block_size, int max_seq_len, int q_dtype,
-                              int kv_dtype, int device, b200_attn_plan_t* plan);
+                              int kv_dtype, int device, const b200_attn_tuning_t* tuning_or_null,
+                              b200_attn_plan_t* plan);
 
-/* Tuning knobs (benchmarking / autotuning; 0 restores the library default).
- *   b200_set_attn_tuning: warps per CTA, ring stages per warp, v1 cluster size.
- *     Also settable through env B200_ATTN_WARPS / B200_ATTN_STAGES / B200_ATTN_CLUSTER.
- *   b200_set_swap_mode: 0 auto, 1 force run-merged cudaMemcpyAsync, 2 force the copy kernel. */
-void b200_set_attn_tuning(int warps, int stages, int cluster);
-void b200_set_swap_mode(int mode);
+/* b200_paged_attention_v1 (version 1; scratch arguments ignored) / _v2 (version 2) with an explicit
+ * launch plan.  Same results as the plain entry points for every plan (tools/sweep_attn.py). */
+int b200_paged_attention_tuned(
+    int version, void* out, float* exp_sums, float* max_logits, void* tmp_out, const void* query,
+    const void* key_cache, const void* value_cache, const int32_t* block_tables,
+    const int32_t* seq_lens, const float* alibi_slopes, int num_seqs, int num_heads,
+    int num_kv_heads, int head_size, int block_size, int max_seq_len, int max_num_blocks_per_seq,
+    int max_num_partitions, int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    float scale, float k_scale, float v_scale, int q_dtype, int kv_dtype,
+    const b200_blocksparse_t* blocksparse, const b200_attn_tuning_t* tuning_or_null, int device,
+    b200_stream_t stream);
+
+/* b200_swap_blocks with the copy mechanism forced: mode 0 = auto (what b200_swap_blocks does),
+ * 1 = run-merged cudaMemcpyAsync, 2 = the gather/scatter kernel (needs pinned host memory). */
+int b200_swap_blocks_mode(const void* src, void* dst, const int64_t* block_mapping_host,
+                          int num_pairs, int64_t block_bytes, int src_device, int dst_device,
+                          int mode, b200_stream_t stream);
 
 /* Number of kernels this library has launched from the calling process (for gpu_launches). */
 int64_t b200_launch_count(void);

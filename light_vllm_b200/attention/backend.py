@@ -7,10 +7,10 @@ backend is FlashAttention (decoding/backends/attention/backends/flash_attn.py:20
   * cache writes  -> reshape_and_cache   (paged layout, optional fused fp8-e4m3 quantisation)
   * decode        -> paged_attention_v1 / v2
   * swap / copy   -> swap_blocks / copy_blocks
-through ``light_vllm_b200._custom_ops``.  Prompt (prefill) tokens without a cached prefix go
-through torch SDPA -- a library call outside the decode hot path, as flash_attn_varlen_func is in
-the reference; prefix-cached / chunked prefill runs the sm_100a ``context_attention_fwd`` kernel
-(SURVEY.md 8f rank 4).
+through ``light_vllm_b200._custom_ops``.  Prompt (prefill) tokens -- with or without a cached prefix,
+with the model's sliding window or ALiBi slopes -- run the package's own sm_100a
+``context_attention_fwd`` kernel (the reference calls flash_attn_varlen_func /
+PagedAttention.forward_prefix there).
 """
 from dataclasses import dataclass
 from typing import Any, Dict, List, Optional, Tuple, Type
@@ -22,6 +22,7 @@ from light_vllm_b200.attention.abstract import (AttentionType, DecodeOnlyAttenti
                                                 DecodeOnlyAttentionMetadata,
                                                 DecodeOnlyAttentionMetadataBuilder)
 from light_vllm_b200.attention.paged_attn import PagedAttention
+from light_vllm_b200.attention.prefix_prefill import context_attention_fwd
 from light_vllm_b200.attention.utils import (compute_slot_mapping,
                                              compute_slot_mapping_start_idx,
                                              is_block_tables_empty, make_tensor_with_pad,
@@ -244,27 +245,62 @@ class PagedB200AttentionImpl(DecodeOnlyAttentionImpl):
                              f"Supported head sizes are: {supported}.")
 
     def _prefill(self, query, key, value, meta) -> torch.Tensor:
-        """Causal self-attention over freshly computed prompt K/V (no cached prefix)."""
+        """Causal self-attention over freshly computed prompt K/V (no cached prefix).
+
+        The reference calls ``flash_attn_varlen_func(causal=True, window_size=self.sliding_window,
+        alibi_slopes=...)`` here (flash_attn.py:522-535) with ``window_size = (W, W)``
+        (flash_attn.py:419-420), i.e. query i sees keys ``i - W <= j <= i``.  Served by the package's
+        own sm_100a prefix-prefill kernel with an empty context (``ctx_len = 0``): its window keeps
+        ``i - j < w`` (prefix_prefill.py:130-143), so ``w = W + 1`` reproduces the flash semantics.
+        ALiBi *and* a window together (no model of the reference's zoo uses both; the Triton kernel
+        drops the window in that case, prefix_prefill.py:712-760) go through a banded-mask SDPA."""
+        n_seq = meta.num_prefills
+        W = self.sliding_window
+        if self.alibi_slopes is not None and W:
+            return self._prefill_masked_sdpa(query, key, value, meta)
+        dev = query.device
+        if meta.seq_lens_tensor is not None:
+            lens = meta.seq_lens_tensor[:n_seq]
+        else:
+            lens = torch.tensor(meta.seq_lens[:n_seq], dtype=torch.int32, device=dev)
+        lens = lens.to(device=dev, dtype=torch.int32)
+        if meta.query_start_loc is not None:
+            starts = meta.query_start_loc[:n_seq].to(device=dev, dtype=torch.int32)
+        else:
+            starts = (torch.cumsum(lens, 0, dtype=torch.int32) - lens)
+        max_len = meta.max_prefill_seq_len or meta.max_query_len or int(lens.max())
+        alibi = self.alibi_slopes
+        if alibi is not None and alibi.device != dev:
+            alibi = self.alibi_slopes = alibi.to(dev)
+        # no cached prefix: one dummy block, never dereferenced (context length 0 for every sequence)
+        x = 16 // query.element_size()
+        kc = torch.empty(1, self.num_kv_heads, self.head_size // x, 16, x, dtype=query.dtype, device=dev)
+        vc = torch.empty(1, self.num_kv_heads, self.head_size, 16, dtype=query.dtype, device=dev)
+        out = torch.empty_like(query)
+        context_attention_fwd(query, key, value, out, kc, vc,
+                              torch.zeros(n_seq, 1, dtype=torch.int32, device=dev), starts, lens,
+                              torch.zeros(n_seq, dtype=torch.int32, device=dev), int(max_len), alibi,
+                              (W + 1) if W else None)
+        return out
+
+    def _prefill_masked_sdpa(self, query, key, value, meta) -> torch.Tensor:
         import torch.nn.functional as F
         out = torch.empty_like(query)
         starts = meta.seq_start_loc.tolist() if meta.seq_lens is None else None
+        slopes = self.alibi_slopes.to(query.device)
+        W = self.sliding_window
         pos = 0
         for i in range(meta.num_prefills):
             n = meta.seq_lens[i] if meta.seq_lens is not None else starts[i + 1] - starts[i]
             q = query[pos:pos + n].transpose(0, 1).unsqueeze(0)          # [1, H, n, D]
             k = key[pos:pos + n].transpose(0, 1).unsqueeze(0)            # [1, KH, n, D]
             v = value[pos:pos + n].transpose(0, 1).unsqueeze(0)
-            if self.alibi_slopes is None:
-                o = F.scaled_dot_product_attention(q, k, v, is_causal=True, scale=self.scale,
-                                                   enable_gqa=self.num_queries_per_kv > 1)
-            else:
-                idx = torch.arange(n, device=query.device)
-                rel = (idx[None, :] - idx[:, None]).to(torch.float32)     # j - i
-                bias = self.alibi_slopes.to(query.device)[:, None, None] * rel[None]
-                bias = bias.masked_fill(rel[None] > 0, float("-inf")).to(query.dtype)
-                o = F.scaled_dot_product_attention(q, k, v, attn_mask=bias.unsqueeze(0),
-                                                   scale=self.scale,
-                                                   enable_gqa=self.num_queries_per_kv > 1)
+            idx = torch.arange(n, device=query.device)
+            rel = (idx[None, :] - idx[:, None]).to(torch.float32)         # j - i
+            bias = slopes[:, None, None] * rel[None]
+            bias = bias.masked_fill((rel[None] > 0) | (rel[None] < -W), float("-inf")).to(query.dtype)
+            o = F.scaled_dot_product_attention(q, k, v, attn_mask=bias.unsqueeze(0), scale=self.scale,
+                                               enable_gqa=self.num_queries_per_kv > 1)
             out[pos:pos + n] = o.squeeze(0).transpose(0, 1)
             pos += n
         return out

@@ -29,7 +29,6 @@ class PagedAttention:
     # v2 scratch is reused across layers/steps of one shape instead of three torch.empty per call
     # (reference :156-166); keyed by (device, stream, dtype, B, H, P, D) -- per stream because the
     # executor may keep two steps in flight on different streams (core/executor.py:62-185).
-    _scratch: Dict[tuple, Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = {}
 
     @staticmethod
     def get_supported_head_sizes() -> List[int]:
@@ -63,21 +62,15 @@ class PagedAttention:
         max_num_partitions = (max_seq_len + _PARTITION_SIZE - 1) // _PARTITION_SIZE
         return max_seq_len <= 8192 and (max_num_partitions == 1 or num_seqs * num_heads > 512)
 
-    @classmethod
-    def _v2_scratch(cls, query: torch.Tensor, max_num_partitions: int):
+    @staticmethod
+    def _v2_scratch(query: torch.Tensor, max_num_partitions: int):
+        """Per-call ``torch.empty`` scratch, exactly as the reference allocates it
+        (paged_attn.py:156-166): the caching allocator makes it cheap, and a CUDA graph that captured
+        the call owns the memory through its graph pool -- nothing cached here can be freed under it."""
         B, H, D = query.shape
-        stream = torch.cuda.current_stream(query.device).cuda_stream
-        key = (query.device, stream, query.dtype, B, H, max_num_partitions, D)
-        buf = cls._scratch.get(key)
-        if buf is None:
-            if len(cls._scratch) > 16:
-                cls._scratch.clear()
-            tmp = torch.empty((B, H, max_num_partitions, D), dtype=query.dtype, device=query.device)
-            exp_sums = torch.empty((B, H, max_num_partitions), dtype=torch.float32,
-                                   device=query.device)
-            buf = (exp_sums, torch.empty_like(exp_sums), tmp)
-            cls._scratch[key] = buf
-        return buf
+        tmp = torch.empty((B, H, max_num_partitions, D), dtype=query.dtype, device=query.device)
+        exp_sums = torch.empty((B, H, max_num_partitions), dtype=torch.float32, device=query.device)
+        return exp_sums, torch.empty_like(exp_sums), tmp
 
     @staticmethod
     def forward_decode(query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,

@@ -8,8 +8,6 @@ import torch
 
 from .. import _lib
 
-_SCRATCH = {}  # per (device, stream): uint8 buffer for the staged new-token pages
-
 
 def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: torch.Tensor,
                           k_cache: torch.Tensor, v_cache: torch.Tensor, b_loc: torch.Tensor,
@@ -17,6 +15,13 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
                           b_ctx_len: torch.Tensor, max_input_len: int,
                           alibi_slopes: Optional[torch.Tensor] = None,
                           sliding_window: Optional[int] = None, use_scratch: bool = True) -> None:
+    """``use_scratch`` (default): the new k/v are first rewritten into page layout in a per-call
+    ``torch.empty`` scratch (graph-pool safe, like the reference's per-call allocations) and streamed
+    through the same bulk-copy ring as the cached context.  That staged mode assumes what
+    ``PagedAttention.forward_prefix`` passes: ``b_start_loc`` = packed exclusive prefix sums of the
+    query lengths (``query_start_loc[:-1]``).  A non-packed ``b_start_loc`` is memory-safe (indices
+    are guarded against the scratch capacity; affected rows come back NaN) but must use
+    ``use_scratch=False``, which accepts arbitrary start locations like the reference kernel."""
     if not q.is_cuda:
         raise RuntimeError("context_attention_fwd: CUDA tensors required (no CPU implementation)")
     if q.dtype not in (torch.float16, torch.bfloat16, torch.float32):
@@ -38,10 +43,7 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
     # scratch for the staged mode (new k/v rewritten into page layout; see csrc/prefix_prefill.cu)
     need = _lib.lib.b200_context_attention_scratch_bytes(k.shape[0], b_seq_len.shape[0], k.shape[1], Lq,
                                                          v_cache.shape[3])
-    skey = (q.device, torch.cuda.current_stream(q.device).cuda_stream)  # stream-ordered reuse
-    scratch = _SCRATCH.get(skey)
-    if scratch is None or scratch.numel() < need:
-        scratch = _SCRATCH[skey] = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=q.device)
+    scratch = torch.empty(max(need, 16) if use_scratch else 16, dtype=torch.uint8, device=q.device)
     rc = _lib.lib.b200_context_attention_fwd(
         q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
         b_loc.data_ptr(), b_start_loc.data_ptr(), b_seq_len.data_ptr(), b_ctx_len.data_ptr(),

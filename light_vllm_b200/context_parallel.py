@@ -111,7 +111,11 @@ class ContextShardGroup:
         self.epoch = 0
         # True: the epoch lives in the exchange buffer (CUDA-graph capturable); all ranks must agree
         self.device_epoch = True
-        self._scratch = {}
+        self._scratch = {}   # grow-only per (B, H, D, dtype); must pre-exist any CUDA-graph capture
+        # outcome of the previous call, mirrored asynchronously into pinned host memory
+        self._mirror = torch.zeros(4, dtype=torch.int32).pin_memory() if torch.cuda.is_available() \
+            else torch.zeros(4, dtype=torch.int32)
+        self._mirror_event = None
 
     # ---- construction ----
     @staticmethod
@@ -165,6 +169,34 @@ class ContextShardGroup:
         _check(_lib.lib.b200_ctx_exchange_status(self._own, self.world, ctypes.byref(s), self.device))
         return int(s.value)
 
+    def set_timeout(self, milliseconds: int) -> None:
+        """How long this rank waits for a peer's publication (default 2000 ms; first calls pay lazy
+        module loads and IPC mapping).  Stored in this group's exchange buffer."""
+        _check(_lib.lib.b200_ctx_exchange_set_timeout(self._own, self.world, int(milliseconds), self.device))
+
+    def clear_status(self) -> None:
+        _check(_lib.lib.b200_ctx_exchange_clear_status(self._own, self.world, self.device))
+        self._mirror.zero_()
+        self._mirror_event = None
+
+    def check(self, wait: bool = False) -> None:
+        """Raise if a previous call timed out waiting for a peer (its output rows were NaN-poisoned
+        by the kernel).  ``wait=False``: only looks at results that have already arrived -- no
+        synchronisation; ``paged_attention`` calls this on entry, so a failure of call n surfaces
+        at call n+1 at the latest.  ``wait=True`` synchronises on the last call first."""
+        ev = self._mirror_event
+        if ev is None:
+            return
+        if wait:
+            ev.synchronize()
+        elif not ev.query():
+            return
+        if int(self._mirror[0]) != 0:
+            raise RuntimeError(
+                f"context-sharded attention: rank {self.rank} timed out waiting for rank "
+                f"{int(self._mirror[0]) - 1} to publish epoch {int(self._mirror[3])}; the outputs of "
+                "that call are NaN on this rank (ContextShardGroup.clear_status() to re-arm)")
+
     # ---- the op ----
     def scratch(self, query: torch.Tensor, max_local_seq_len: int):
         B, H, D = query.shape
@@ -187,6 +219,7 @@ class ContextShardGroup:
         call it, in the same order.  ``phases=1`` (partition pass + publish) followed later by
         ``phases=2`` (wait + merge, same arguments) is the split-phase form of the default 3."""
         assert query.is_cuda and out.is_contiguous() and query.stride(-1) == 1
+        self.check()
         B, H, D = query.shape
         assert B * H <= self.max_pairs and D == self.head_size
         es, ml, tmp = self.scratch(query, max_local_seq_len)
@@ -206,3 +239,9 @@ class ContextShardGroup:
             query.device.index if query.device.index is not None else torch.cuda.current_device(),
             torch.cuda.current_stream(query.device).cuda_stream)
         _check(rc)
+        if phases & 2 and not torch.cuda.is_current_stream_capturing():
+            stream = torch.cuda.current_stream(query.device)
+            _check(_lib.lib.b200_ctx_exchange_status_async(self._own, self.world, self._mirror.data_ptr(),
+                                                           self.device, stream.cuda_stream))
+            self._mirror_event = torch.cuda.Event()
+            self._mirror_event.record(stream)

@@ -446,10 +446,6 @@ extern "C" int b200_copy_blocks(void* const* key_cache_ptrs, void* const* value_
   return B200_OK;
 }
 
-// 0 = auto (kernel when both sides are device-addressable, else memcpy), 1 = force run-merged
-// cudaMemcpyAsync, 2 = force kernel.  Tuning / benchmarking knob.
-static std::atomic<int> g_swap_mode{0};
-extern "C" void b200_set_swap_mode(int mode) { g_swap_mode.store(mode); }
 
 // Resolve a pointer to something a kernel running on `device` can dereference, or nullptr.
 static const void* device_addressable(const void* p, int p_device) {
@@ -464,9 +460,11 @@ static const void* device_addressable(const void* p, int p_device) {
   return nullptr;  // pageable host memory
 }
 
-extern "C" int b200_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host,
-                                int num_pairs, int64_t block_bytes, int src_device, int dst_device,
-                                b200_stream_t stream_) {
+// mode: 0 = auto (gather kernel when both sides are device-addressable, else memcpy), 1 = force
+// run-merged cudaMemcpyAsync, 2 = force the kernel.  A per-call argument; no state is kept.
+extern "C" int b200_swap_blocks_mode(const void* src, void* dst, const int64_t* block_mapping_host,
+                                     int num_pairs, int64_t block_bytes, int src_device,
+                                     int dst_device, int mode, b200_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   B200_CHECK_ARG(num_pairs >= 0 && block_bytes > 0, "swap_blocks: bad sizes");
   cudaMemcpyKind kind;
@@ -485,7 +483,7 @@ extern "C" int b200_swap_blocks(const void* src, void* dst, const int64_t* block
   DeviceGuard guard(src_device >= 0 ? src_device : dst_device);
   B200_CUDA_OK(guard.err);
 
-  const int mode = g_swap_mode.load();
+  B200_CHECK_ARG(mode >= 0 && mode <= 2, "swap_blocks: mode must be 0, 1 or 2");
   const void* src_dev = device_addressable(src, src_device);
   void* dst_dev = const_cast<void*>(device_addressable(dst, dst_device));
   const bool kernel_ok = src_dev && dst_dev;
@@ -528,6 +526,13 @@ extern "C" int b200_swap_blocks(const void* src, void* dst, const int64_t* block
     i += run;
   }
   return B200_OK;
+}
+
+extern "C" int b200_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host,
+                                int num_pairs, int64_t block_bytes, int src_device, int dst_device,
+                                b200_stream_t stream) {
+  return b200_swap_blocks_mode(src, dst, block_mapping_host, num_pairs, block_bytes, src_device,
+                               dst_device, 0, stream);
 }
 
 extern "C" int b200_convert_fp8(void* dst, const void* src, int64_t numel, float scale,

@@ -10,7 +10,10 @@
 //
 // Exchange buffer layout (identical on every rank; b200_ctx_exchange_bytes):
 //   u32   flags[world][kCtxMaxCtas]            epoch last published by (source rank, CTA)
-//   u32   status[32]                           [0] != 0: a wait timed out (peer never arrived)
+//   u32   status[32]                           [0] != 0: a wait timed out (1 + rank that never arrived);
+//                                              [1] device-managed epoch, [2] its completion counter,
+//                                              [3] epoch of the call that timed out, [4] timeout in ms
+//                                              (0 = 2000; b200_ctx_exchange_set_timeout)
 //   float data[2][world][max_pairs][D + 4]     row = {m, l, 0, 0, o[0..D)}; slot = epoch & 1
 // Two data slots suffice: a rank can only be one call ahead of its slowest peer, because call
 // n+1 cannot finish before every peer has published call n+1, which it does after reading call n.
@@ -53,6 +56,8 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
                           long long timeout_cycles) {
   extern __shared__ float wsm[];  // [4 warps][head_size] partial folds
   __shared__ uint32_t epoch_s;
+  __shared__ int timed_out_s;
+  __shared__ long long timeout_s;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   // epoch == 0: device-managed.  The call's epoch is the counter in this rank's own header + 1; the
@@ -60,8 +65,14 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
   // replayed (a host-supplied epoch would be frozen into the graph).
   uint32_t* hdr_epoch = reinterpret_cast<uint32_t*>(peers.buf[rank]) + world * kCtxMaxCtas + 1;
   const bool device_epoch = epoch == 0;
-  if (threadIdx.x == 0) epoch_s = device_epoch ? __ldcg(hdr_epoch) + 1u : epoch;
+  if (threadIdx.x == 0) {
+    epoch_s = device_epoch ? __ldcg(hdr_epoch) + 1u : epoch;
+    timed_out_s = 0;
+    const uint32_t ms = __ldcg(hdr_epoch + 3);  // status[4]: per-group timeout, 0 = default
+    timeout_s = ms ? (long long)ms * 2000000LL : timeout_cycles;  // ~2 GHz SM clock
+  }
   __syncthreads();
+  timeout_cycles = timeout_s;
   epoch = epoch_s;
   const int row_floats = head_size + kCtxRowPad;
   const size_t hdr = ctx_header_bytes(world);
@@ -127,7 +138,9 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
     const long long t0 = clock64();
     while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
       if (clock64() - t0 > timeout_cycles) {
-        atomicExch(reinterpret_cast<unsigned int*>(mine) + world * kCtxMaxCtas, 1u + threadIdx.x);
+        unsigned int* st = reinterpret_cast<unsigned int*>(mine) + world * kCtxMaxCtas;
+        if (atomicCAS(st, 0u, 1u + threadIdx.x) == 0u) st[3] = epoch;  // first failure: who and when
+        timed_out_s = 1;
         break;
       }
       __nanosleep(64);
@@ -135,7 +148,15 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
   }
   __syncthreads();
   const float* data = reinterpret_cast<const float*>(mine + hdr) + slot_off;
+  const bool poisoned = timed_out_s != 0;
   for (int pair = blockIdx.x; pair < total_pairs; pair += gridDim.x) {
+    if (poisoned) {
+      // A peer never published this epoch: its slot is stale or half written.  Fail loudly in the
+      // data -- NaN rows -- instead of merging it (the status word says who and which epoch).
+      T* o = out + (int64_t)pair * head_size;
+      for (int d = threadIdx.x; d < head_size; d += blockDim.x) o[d] = from_f32<T>(__int_as_float(0x7fc00000));
+      continue;
+    }
     float M = kNegInf;
     for (int r = 0; r < world; ++r) {
       const float2 st = __ldcg(reinterpret_cast<const float2*>(data + ((size_t)r * max_pairs + pair) * row_floats));
@@ -190,8 +211,8 @@ int launch_ctx_exchange(void* out, const float* exp_sums, const float* max_logit
     peers.buf[r] = static_cast<unsigned char*>(exchange_bufs[r]);
   }
   int blocks = (int)pairs;
-  static const int cap = [] { const char* e = getenv("B200_CTX_MAX_CTAS"); int v = e ? atoi(e) : 0; return v > 0 && v <= kCtxMaxCtas ? v : 148; }();
-  if (blocks > cap) blocks = cap;  // same on every rank (flags are per CTA); all co-resident
+  const int cap = 148;  // same on every rank (flags are per CTA); all CTAs co-resident
+  if (blocks > cap) blocks = cap;
   const int wstride = head_size;
   const size_t wsmem = (size_t)4 * head_size * sizeof(float);
   (void)parts;
@@ -264,6 +285,41 @@ extern "C" int b200_peer_close(void* ptr, int device) {
   DeviceGuard guard(device);
   B200_CUDA_OK(guard.err);
   B200_CUDA_OK(cudaIpcCloseMemHandle(ptr));
+  return B200_OK;
+}
+
+// Asynchronous copy of {status, -, -, epoch of the failing call} (4 words) into pinned host memory on
+// `stream`: lets the host check the PREVIOUS call's outcome at the next call without synchronising.
+extern "C" int b200_ctx_exchange_status_async(const void* local_buf, int world, int32_t* pinned_host4,
+                                              int device, b200_stream_t stream) {
+  B200_CHECK_ARG(local_buf && pinned_host4, "ctx_exchange_status_async: bad arguments");
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  B200_CUDA_OK(cudaMemcpyAsync(pinned_host4, static_cast<const unsigned char*>(local_buf) +
+                                                 (size_t)world * kCtxMaxCtas * 4,
+                               16, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return B200_OK;
+}
+
+// Per-group wait timeout (milliseconds at ~2 GHz; 0 restores the 2 s default) and status reset.
+// State lives in the group's own exchange buffer, not in the library.
+extern "C" int b200_ctx_exchange_set_timeout(void* local_buf, int world, int timeout_ms, int device) {
+  B200_CHECK_ARG(local_buf && timeout_ms >= 0, "ctx_exchange_set_timeout: bad arguments");
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  const uint32_t ms = (uint32_t)timeout_ms;
+  B200_CUDA_OK(cudaMemcpy(static_cast<unsigned char*>(local_buf) + ((size_t)world * kCtxMaxCtas + 4) * 4,
+                          &ms, 4, cudaMemcpyHostToDevice));
+  return B200_OK;
+}
+extern "C" int b200_ctx_exchange_clear_status(void* local_buf, int world, int device) {
+  B200_CHECK_ARG(local_buf, "ctx_exchange_clear_status: bad arguments");
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  const uint32_t z = 0;
+  unsigned char* st = static_cast<unsigned char*>(local_buf) + (size_t)world * kCtxMaxCtas * 4;
+  B200_CUDA_OK(cudaMemcpy(st, &z, 4, cudaMemcpyHostToDevice));
+  B200_CUDA_OK(cudaMemcpy(st + 12, &z, 4, cudaMemcpyHostToDevice));
   return B200_OK;
 }
 

@@ -105,23 +105,12 @@ paged_attention_v2_reduce_kernel(T* __restrict__ out, const float* __restrict__ 
 // ---------------------------------------------------------------------------------------
 // launch planning
 // ---------------------------------------------------------------------------------------
-static int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
-}
-// Tuning knobs: env B200_ATTN_WARPS / B200_ATTN_STAGES / B200_ATTN_CLUSTER at first use, or
-// b200_set_attn_tuning() at run time (0 = library default).
+// Per-call launch overrides (b200_attn_tuning_t; 0 = library default).  They arrive as an argument of
+// b200_paged_attention_tuned / b200_paged_attention_plan only: the library keeps no mutable state
+// between calls and reads no environment variables (thread-per-GPU callers).
 struct Knobs {
-  std::atomic<int> warps, stages, cluster;
-  Knobs()
-      : warps(env_int("B200_ATTN_WARPS", 0)),
-        stages(env_int("B200_ATTN_STAGES", 0)),
-        cluster(env_int("B200_ATTN_CLUSTER", 0)) {}
+  int warps = 0, stages = 0, cluster = 0;
 };
-static Knobs& knobs() {
-  static Knobs k;
-  return k;
-}
 
 struct Plan {
   AttnEntry entry;
@@ -133,7 +122,7 @@ struct Plan {
 
 static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num_kv_heads,
                      int head_size, int block_size, int max_seq_len, int q_dtype, int kv_dtype,
-                     int device) {
+                     int device, const Knobs& kn) {
   B200_CHECK_ARG(num_kv_heads > 0 && num_heads > 0 && num_heads % num_kv_heads == 0,
                  "num_heads (%d) must be a positive multiple of num_kv_heads (%d)", num_heads,
                  num_kv_heads);
@@ -183,7 +172,7 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
   // shared memory, between 2 and 4 stages (one stage = one K page + one V page).
   const int es = kv_dtype == B200_KV_AUTO ? (q_dtype == B200_DT_F32 ? 4 : 2) : 1;
   const size_t stage_bytes = (size_t)2 * head_size * block_size * es;
-  pl.nwarps = knobs().warps.load();
+  pl.nwarps = kn.warps;
   if (pl.nwarps < 1) pl.nwarps = 4;
   if (pl.nwarps > 8) pl.nwarps = 8;
   if (q_dtype == B200_DT_F32) {  // 128-thread kernel; fp32 pages are up to 32 KiB each
@@ -191,7 +180,7 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
     while (pl.nwarps > 1 && (size_t)pl.nwarps * 2 * stage_bytes > (size_t)200 * 1024) pl.nwarps /= 2;
   }
   const long long base = (long long)num_seqs * num_kv_heads * pl.gchunks;  // CTAs before any split
-  int ns = knobs().stages.load();
+  int ns = kn.stages;
   if (ns <= 0) {
     // candidate A: ring that lets three CTAs share an SM (2..4 stages); candidate B: a deeper ring
     // with two CTAs per SM.  A wins whenever the grid runs for many waves or fits in one; B wins
@@ -229,7 +218,7 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
   // (profiles/r1_sweep_grid.md: B=16 -> 2, B=32 -> 1, B<=4 -> 8 are the measured optima).
   pl.cluster = 1;
   if (version == 1) {
-    const int forced = knobs().cluster.load();
+    const int forced = kn.cluster;
     if (q_dtype == B200_DT_F32) {
       pl.cluster = 1;  // the fp32 kernel has no cluster merge: v1 runs unsplit
     } else if (forced > 0) {
@@ -258,7 +247,7 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
     if (want > p512) want = p512;
     int m = (int)(p512 / want);
     if (m < 1) m = 1;
-    const int forced = knobs().cluster.load();  // tuning: "cluster" knob = forced m for v2
+    const int forced = kn.cluster;  // tuning: "cluster" knob = forced m for v2
     if (forced > 0) m = forced;
     pl.v2_partition_tokens = kPartitionSize * m;
     pl.v2_parts = (p512 + m - 1) / m;
@@ -275,7 +264,7 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
                          int64_t kv_block_stride, int64_t kv_head_stride, float scale,
                          float k_scale, float v_scale, int q_dtype, int kv_dtype,
                          const b200_blocksparse_t* bsp, int device, cudaStream_t stream,
-                         const CtxShardArgs* ctx = nullptr) {
+                         const CtxShardArgs* ctx = nullptr, const Knobs& kn = Knobs()) {
   B200_CHECK_ARG(num_seqs >= 0 && head_size > 0 && block_size > 0 && max_seq_len >= 0,
                  "paged_attention: bad sizes");
   if (num_seqs == 0) return B200_OK;
@@ -287,7 +276,7 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
 
   Plan pl;
   int rc = make_plan(pl, version, num_seqs, num_heads, num_kv_heads, head_size, block_size,
-                     max_seq_len, q_dtype, kv_dtype, dev);
+                     max_seq_len, q_dtype, kv_dtype, dev, kn);
   if (rc != B200_OK) return rc;
 
   const int es = kv_dtype == B200_KV_AUTO ? (q_dtype == B200_DT_F32 ? 4 : 2) : 1;
@@ -443,9 +432,40 @@ extern "C" int b200_paged_attention_ctx_shard(
                        &ctx);
 }
 
+static Knobs to_knobs(const b200_attn_tuning_t* t) {
+  Knobs k;
+  if (t) {
+    k.warps = t->num_warps;
+    k.stages = t->num_stages;
+    k.cluster = t->split;
+  }
+  return k;
+}
+
+extern "C" int b200_paged_attention_tuned(
+    int version, void* out, float* exp_sums, float* max_logits, void* tmp_out, const void* query,
+    const void* key_cache, const void* value_cache, const int32_t* block_tables,
+    const int32_t* seq_lens, const float* alibi_slopes, int num_seqs, int num_heads,
+    int num_kv_heads, int head_size, int block_size, int max_seq_len, int max_num_blocks_per_seq,
+    int max_num_partitions, int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    float scale, float k_scale, float v_scale, int q_dtype, int kv_dtype,
+    const b200_blocksparse_t* blocksparse, const b200_attn_tuning_t* tuning, int device,
+    b200_stream_t stream) {
+  B200_CHECK_ARG(version == 1 || version == 2, "paged_attention_tuned: version must be 1 or 2");
+  if (version == 2)
+    B200_CHECK_ARG(exp_sums && max_logits && tmp_out, "paged_attention_v2: scratch tensors required");
+  return run_attention(version, out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
+                       block_tables, seq_lens, alibi_slopes, num_seqs, num_heads, num_kv_heads,
+                       head_size, block_size, max_seq_len, max_num_blocks_per_seq,
+                       version == 2 ? max_num_partitions : 0, q_stride, kv_block_stride,
+                       kv_head_stride, scale, k_scale, v_scale, q_dtype, kv_dtype, blocksparse,
+                       device, (cudaStream_t)stream, nullptr, to_knobs(tuning));
+}
+
 extern "C" int b200_paged_attention_plan(int version, int num_seqs, int num_heads, int num_kv_heads,
                                          int head_size, int block_size, int max_seq_len,
                                          int q_dtype, int kv_dtype, int device,
+                                         const b200_attn_tuning_t* tuning,
                                          b200_attn_plan_t* plan) {
   B200_CHECK_ARG(plan != nullptr, "plan must not be null");
   DeviceGuard guard(device);
@@ -454,7 +474,7 @@ extern "C" int b200_paged_attention_plan(int version, int num_seqs, int num_head
   if (dev < 0) B200_CUDA_OK(cudaGetDevice(&dev));
   Plan pl;
   int rc = make_plan(pl, version, num_seqs, num_heads, num_kv_heads, head_size, block_size,
-                     max_seq_len, q_dtype, kv_dtype, dev);
+                     max_seq_len, q_dtype, kv_dtype, dev, to_knobs(tuning));
   if (rc != B200_OK) return rc;
   plan->cluster_size = pl.cluster;
   plan->num_warps = pl.nwarps;
@@ -467,8 +487,3 @@ extern "C" int b200_paged_attention_plan(int version, int num_seqs, int num_head
   return B200_OK;
 }
 
-extern "C" void b200_set_attn_tuning(int warps, int stages, int cluster) {
-  knobs().warps.store(warps);
-  knobs().stages.store(stages);
-  knobs().cluster.store(cluster);
-}

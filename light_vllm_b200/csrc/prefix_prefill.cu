@@ -28,6 +28,7 @@ struct PrefixParams {
   const unsigned char* kv_scratch;  // new k/v pre-staged as pages (prefix_stage_kv_kernel) or NULL
   int num_heads, num_kv_heads, group, max_blocks_per_seq, sliding_window, tok_tile, num_stages,
       stage_shift;
+  int64_t scratch_slices;  // capacity of kv_scratch in (slice, all kv heads) units: staged indices are guarded
   int64_t q_s0, q_s1, k_s0, k_s1, v_s0, v_s1, o_s0, o_s1, kc_bs, kc_hs, vc_bs, vc_hs;
   float scale_log2;
 };
@@ -62,6 +63,17 @@ context_attention_kernel(const __grid_constant__ PrefixParams p) {
   const int G = p.group;
   const int tile_tokens = min(p.tok_tile, qlen - m0);
   const int W = p.sliding_window;
+  // Staged mode indexes the scratch by start_loc (device data the host cannot verify): a start_loc that
+  // is not the packed prefix sum would point past the scratch.  Never read out of bounds -- poison this
+  // CTA's output rows with NaN instead (loud in the data) and leave.
+  if (p.kv_scratch != nullptr &&
+      (start < 0 || (int64_t)(start / BS) + seq + (m0 + tile_tokens - 1) / BS >= p.scratch_slices)) {
+    for (int r = threadIdx.x; r < tile_tokens * G; r += blockDim.x) {
+      T* orow = static_cast<T*>(p.out) + (start + m0 + r / G) * p.o_s0 + (int64_t)(kvh * G + r % G) * p.o_s1;
+      for (int d = 0; d < D; ++d) orow[d] = from_f32<T>(__int_as_float(0x7fc00000));
+    }
+    return;
+  }
 
   unsigned char* ring = smem;  // [NS stages][K page | V page], then the mbarriers, then slack
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)NS * STAGE_BYTES);
@@ -480,7 +492,9 @@ __global__ void __launch_bounds__(128) prefix_stage_kv_kernel(const __grid_const
       *reinterpret_cast<uint16_t*>(sm + PAGE_BYTES + (size_t)((c * 8 + x) * BS + t) * 2) = e[x];
   }
   __syncthreads();
-  unsigned char* dst = scratch + (((int64_t)(start / BS) + seq + sl) * p.num_kv_heads + kvh) * (2 * PAGE_BYTES);
+  const int64_t slice = (int64_t)(start / BS) + seq + sl;
+  if (start < 0 || slice >= p.scratch_slices) return;  // non-packed start_loc: never write out of bounds
+  unsigned char* dst = scratch + (slice * p.num_kv_heads + kvh) * (2 * PAGE_BYTES);
   for (int idx = threadIdx.x; idx < 2 * PAGE_BYTES / 16; idx += blockDim.x)
     reinterpret_cast<uint4*>(dst)[idx] = reinterpret_cast<const uint4*>(sm)[idx];
 }
@@ -724,6 +738,7 @@ extern "C" int b200_context_attention_fwd(
                   (reinterpret_cast<uintptr_t>(kv_scratch) & 15) == 0)
                      ? static_cast<const unsigned char*>(kv_scratch)
                      : nullptr;
+  p.scratch_slices = p.kv_scratch ? kv_scratch_bytes / ((int64_t)num_kv_heads * 2 * head_size * block_size * 2) : 0;
   if (dtype == B200_DT_F32) {
     B200_CHECK_ARG(head_size % 4 == 0 && head_size <= 256 && (reinterpret_cast<uintptr_t>(q) & 15) == 0 &&
                        q_stride0 % 4 == 0 && q_stride1 % 4 == 0,

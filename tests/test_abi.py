@@ -23,7 +23,7 @@ def test_header_symbols_exported():
     for n in names:
         assert hasattr(_lib.lib, n), f"{n} declared in include/b200_paged.h but not exported"
     assert set(names) == set(_lib.ABI_SYMBOLS)
-    assert _lib.lib.b200_abi_version() == 1
+    assert _lib.lib.b200_abi_version() == 2
 
 
 def test_parse_kv_cache_dtype():

@@ -124,12 +124,11 @@ def test_swap_blocks(ops, oracle, direction, mode, pinned):
     host = (lambda t: t.pin_memory()) if pinned else (lambda t: t.clone())
     s = src.cuda() if direction in ("d2h", "d2d") else host(src)
     d = dst.cuda() if direction in ("h2d", "d2d") else host(dst)
-    _lib.set_swap_mode(mode)
-    try:
+    if mode == 0:    # the op, as the engine calls it
         ops.swap_blocks(s.view(torch.float16), d.view(torch.float16), mapping)
-        torch.cuda.synchronize()
-    finally:
-        _lib.set_swap_mode(0)
+    else:            # copy mechanism forced: a per-call argument of the C ABI (no global state)
+        _lib.swap_blocks_mode(s.view(torch.float16), d.view(torch.float16), mapping, mode)
+    torch.cuda.synchronize()
     assert torch.equal(d.cpu(), want)
     with pytest.raises(RuntimeError, match="block_mapping must be on CPU"):
         ops.swap_blocks(src.cuda(), dst.cuda(), mapping.cuda())

@@ -245,11 +245,23 @@ def test_missing_peer_times_out_instead_of_hanging():
     groups = ContextShardGroup.create_local(2, 8, 128, 0)
     try:
         bt, ll, mx = sh.shard_batch(case["block_tables"], [64], 0)
-        out = torch.empty_like(d["query"])
-        groups[0].paged_attention(out, d["query"], d["key_cache"], d["value_cache"], 2,
-                                  case["scale"], bt.cuda(), ll.cuda(), 16, mx)  # rank 1 never calls
+        out = torch.zeros_like(d["query"])
+        groups[0].set_timeout(50)  # per-group, lives in the exchange buffer (default 2 s)
+        args = (out, d["query"], d["key_cache"], d["value_cache"], 2, case["scale"], bt.cuda(),
+                ll.cuda(), 16, mx)
+        groups[0].paged_attention(*args)  # rank 1 never calls
         torch.cuda.synchronize()
         assert groups[0].status() == 2  # 1 + the rank that never published
+        # loud in the data: the stale peer slot is NOT merged, the rows come back NaN ...
+        assert torch.isnan(out.float()).all()
+        # ... and loud on the host: the next call (or check()) raises, naming the rank and the epoch
+        with pytest.raises(RuntimeError, match="timed out waiting for rank 1 to publish epoch 1"):
+            groups[0].paged_attention(*args)
+        with pytest.raises(RuntimeError, match="timed out"):
+            groups[0].check(wait=True)
+        groups[0].clear_status()
+        groups[0].check(wait=True)
+        assert groups[0].status() == 0
     finally:
         for g in groups:
             g.close()

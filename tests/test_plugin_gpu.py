@@ -155,4 +155,45 @@ def test_forward_decode_v2_path_and_scratch_reuse():
                                             g["block_tables"], g["seq_lens"], max(lens), "auto", 2,
                                             c["scale"], None, 1.0, 1.0)
     assert (out.double().cpu() - naive_attention(c)).abs().max() <= 2e-3
-    assert len(PagedAttention._scratch) >= 1
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float16, 2e-3), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("window,alibi", [(None, False), (24, False), (100, False), (None, True), (24, True)])
+def test_prefill_sliding_window_and_alibi(dtype, tol, window, alibi):
+    """Prompt-only prefill (no cached prefix) with prompt_len > window: the reference passes
+    window_size=(W, W) to flash_attn_varlen_func (flash_attn.py:419-420,522-535), i.e. query i sees
+    keys i-W <= j <= i; the slot mapping drops older tokens, so decode agrees afterwards."""
+    H, KH, D = 8, 2, 64
+    lens = [70, 1, 33, 130]
+    T = sum(lens)
+    g = torch.Generator().manual_seed(5)
+    qkv = ((torch.rand(T, (H + 2 * KH) * D, generator=g) * 2 - 1) * 0.5).to(dtype).cuda()
+    q, k, v = qkv.split([H * D, KH * D, KH * D], dim=-1)
+    slopes = [2.0 ** (-(i + 1)) for i in range(H)] if alibi else None
+    impl = PagedB200AttentionBackend.get_impl_cls()(H, D, D ** -0.5, KH, slopes, window, "auto")
+    starts = torch.tensor([0] + lens, dtype=torch.int32).cumsum(0).int()
+    meta = PagedB200AttentionMetadata(
+        num_prefills=len(lens), num_prefill_tokens=T, num_decode_tokens=0,
+        slot_mapping=torch.full((T,), -1, dtype=torch.long), seq_lens=lens,
+        seq_lens_tensor=torch.tensor(lens, dtype=torch.int), max_query_len=max(lens),
+        max_prefill_seq_len=max(lens), max_decode_seq_len=0, query_start_loc=starts,
+        seq_start_loc=starts, context_lens_tensor=torch.zeros(len(lens), dtype=torch.int),
+        block_tables=torch.zeros(len(lens), 0, dtype=torch.int), use_cuda_graph=False).to("cuda")
+    out = impl.forward(q, k, v, None, meta).view(T, H, D).double().cpu()
+    qd, kd, vd = (t.double().cpu() for t in (q.reshape(T, H, D), k.reshape(T, KH, D), v.reshape(T, KH, D)))
+    pos = 0
+    for n in lens:
+        i = torch.arange(n)
+        rel = (i[None, :] - i[:, None]).double()                      # j - i
+        mask = rel > 0
+        if window:
+            mask = mask | (rel < -window)
+        for h in range(H):
+            logits = (qd[pos:pos + n, h] @ kd[pos:pos + n, h // (H // KH)].T) * D ** -0.5
+            if alibi:
+                logits = logits + slopes[h] * rel
+            p_ = torch.softmax(logits.masked_fill(mask, float("-inf")), dim=-1)
+            want = p_ @ vd[pos:pos + n, h // (H // KH)]
+            err = (out[pos:pos + n, h] - want).abs().max().item()
+            assert err <= tol, f"len {n} head {h}: {err}"
+        pos += n

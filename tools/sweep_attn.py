@@ -74,7 +74,14 @@ def main():
             mod.paged_attention_v2(out, *scratch, q, kc, vc, KH, scale, bt, sl, BS, ctx, None, kv,
                                    ks, vs, 0, 0, 0, 64, 0)
 
-    def time_it(mod):
+    def tuned_call(tuning):
+        def f(_mod, l):
+            kc, vc = split[l]
+            _lib.paged_attention_tuned(c["version"], out, scratch if c["version"] == 2 else None, q,
+                                       kc, vc, KH, scale, bt, sl, BS, ctx, kv, ks, vs, tuning)
+        return f
+
+    def time_it(mod, call=call):
         for l in range(L):
             call(mod, l)
         torch.cuda.synchronize()
@@ -89,16 +96,14 @@ def main():
     ab = algorithmic_bytes_attention(c)
     for plan in args.plans.split(";"):
         w, s, cl = [int(x) for x in plan.split(",")]
-        _lib.set_attn_tuning(w, s, cl)
         try:
-            us = time_it(ops)
-            info = _lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, 0)
+            us = time_it(ops, tuned_call((w, s, cl)))
+            info = _lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, 0, (w, s, cl))
             print(json.dumps({"impl": "b200", "config": args.config, "v": c["version"], "B": B,
                               "ctx": ctx, "plan": plan, "us": round(us, 2),
                               "GBps": round(ab / us / 1e3, 1), "resolved": info}), flush=True)
         except RuntimeError as e:
             print(json.dumps({"impl": "b200", "plan": plan, "error": str(e)[:200]}), flush=True)
-    _lib.set_attn_tuning(0, 0, 0)
     if args.ref:
         from oracle import ref
         rC, _ = ref.ref_cuda()
