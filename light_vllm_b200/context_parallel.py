@@ -185,8 +185,8 @@ class ContextShardGroup:
         synchronisation; ``paged_attention`` calls this on entry, so a failure of call n surfaces
         at call n+1 at the latest.  ``wait=True`` synchronises on the last call first."""
         ev = self._mirror_event
-        if ev is None:
-            return
+        if ev is None or torch.cuda.is_current_stream_capturing():
+            return  # (event queries are not allowed while a stream of this thread is capturing)
         if wait:
             ev.synchronize()
         elif not ev.query():
