@@ -253,6 +253,24 @@ int b200_context_attention_fwd(
     int64_t vc_block_stride, int64_t vc_head_stride, const float* alibi_slopes, int sliding_window,
     float scale, void* kv_scratch, int64_t kv_scratch_bytes, int64_t num_tokens, int dtype,
     int device, b200_stream_t stream);
+/* Same call with the tile loop chosen by the caller (tests, benchmarks, autotuning; per call, no
+ * global state).  AUTO = b200_context_attention_fwd.  MMA_SYNC: csrc/prefix_prefill.cu (every head size,
+ * ALiBi, sliding window, fp32 on CUDA cores).  TCGEN05: csrc/prefix_prefill_umma.cuh (tcgen05.mma with
+ * TMEM accumulators, 256-row tiles; head size 128, fp16 / bf16, no ALiBi / window, needs kv_scratch and
+ * 16-byte aligned q / out rows -- B200_ERR_UNSUPPORTED otherwise). */
+#define B200_PREFIX_PATH_AUTO 0
+#define B200_PREFIX_PATH_MMA_SYNC 1
+#define B200_PREFIX_PATH_TCGEN05 2
+int b200_context_attention_fwd_path(
+    const void* q, const void* k, const void* v, void* out, const void* key_cache,
+    const void* value_cache, const int32_t* block_tables, const int32_t* start_loc,
+    const int32_t* seq_lens, const int32_t* ctx_lens, int num_seqs, int num_heads, int num_kv_heads,
+    int head_size, int block_size, int max_blocks_per_seq, int max_query_len, int64_t q_stride0,
+    int64_t q_stride1, int64_t k_stride0, int64_t k_stride1, int64_t v_stride0, int64_t v_stride1,
+    int64_t o_stride0, int64_t o_stride1, int64_t kc_block_stride, int64_t kc_head_stride,
+    int64_t vc_block_stride, int64_t vc_head_stride, const float* alibi_slopes, int sliding_window,
+    float scale, void* kv_scratch, int64_t kv_scratch_bytes, int64_t num_tokens, int dtype,
+    int device, b200_stream_t stream, int path);
 int64_t b200_context_attention_scratch_bytes(int64_t num_tokens, int num_seqs, int num_kv_heads,
                                              int head_size, int block_size);
 

@@ -54,6 +54,7 @@ ABI_SYMBOLS = (
     "b200_peer_open",
     "b200_peer_close",
     "b200_context_attention_fwd",
+    "b200_context_attention_fwd_path",
     "b200_context_attention_scratch_bytes",
 )
 
@@ -99,6 +100,7 @@ def _load():
     lib.b200_swap_blocks_mode.argtypes = [vp, vp, vp, i32, i64, i32, i32, i32, vp]
     lib.b200_context_attention_fwd.argtypes = (
         [vp] * 10 + [i32] * 7 + [i64] * 12 + [vp, i32, f32, vp, i64, i64, i32, i32, vp])
+    lib.b200_context_attention_fwd_path.argtypes = lib.b200_context_attention_fwd.argtypes + [i32]
     lib.b200_context_attention_scratch_bytes.restype = ctypes.c_int64
     lib.b200_context_attention_scratch_bytes.argtypes = [i64, i32, i32, i32, i32]
     lib.b200_ctx_exchange_status.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_int32), i32]
@@ -126,6 +128,7 @@ def last_error() -> str:
     return lib.b200_last_error().decode()
 
 
+PREFIX_PATHS = {"auto": 0, "mma_sync": 1, "tcgen05": 2}  # B200_PREFIX_PATH_*
 _DT = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
 
 

@@ -14,8 +14,14 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
                           b_start_loc: torch.Tensor, b_seq_len: torch.Tensor,
                           b_ctx_len: torch.Tensor, max_input_len: int,
                           alibi_slopes: Optional[torch.Tensor] = None,
-                          sliding_window: Optional[int] = None, use_scratch: bool = True) -> None:
-    """``use_scratch`` (default): the new k/v are first rewritten into page layout in a per-call
+                          sliding_window: Optional[int] = None, use_scratch: bool = True,
+                          path: str = "auto") -> None:
+    """``path``: ``"auto"`` (default) lets the library pick the tile loop -- the tcgen05 / TMEM kernel
+    (``csrc/prefix_prefill_umma.cuh``) for head size 128 fp16 / bf16 without ALiBi / window once a
+    sequence brings >= 128 (token, head) rows, the ``mma.sync`` kernel otherwise; ``"tcgen05"`` /
+    ``"mma_sync"`` force one (tests, benchmarks; unsupported combinations raise).
+
+    ``use_scratch`` (default): the new k/v are first rewritten into page layout in a per-call
     ``torch.empty`` scratch (graph-pool safe, like the reference's per-call allocations) and streamed
     through the same bulk-copy ring as the cached context.  That staged mode assumes what
     ``PagedAttention.forward_prefix`` passes: ``b_start_loc`` = packed exclusive prefix sums of the
@@ -44,7 +50,7 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
     need = _lib.lib.b200_context_attention_scratch_bytes(k.shape[0], b_seq_len.shape[0], k.shape[1], Lq,
                                                          v_cache.shape[3])
     scratch = torch.empty(max(need, 16) if use_scratch else 16, dtype=torch.uint8, device=q.device)
-    rc = _lib.lib.b200_context_attention_fwd(
+    rc = _lib.lib.b200_context_attention_fwd_path(
         q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
         b_loc.data_ptr(), b_start_loc.data_ptr(), b_seq_len.data_ptr(), b_ctx_len.data_ptr(),
         b_seq_len.shape[0], q.shape[1], k.shape[1], Lq, v_cache.shape[3], b_loc.stride(0),
@@ -54,6 +60,6 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
         int(sliding_window) if sliding_window and sliding_window > 0 else 0,
         ctypes.c_float(1.0 / (Lq ** 0.5)), scratch.data_ptr() if use_scratch else None, scratch.numel(),
         k.shape[0], _lib._DT[q.dtype], q.device.index,
-        torch.cuda.current_stream(q.device).cuda_stream)
+        torch.cuda.current_stream(q.device).cuda_stream, _lib.PREFIX_PATHS[path])
     if rc != 0:
         raise RuntimeError(_lib.last_error())

@@ -14,24 +14,12 @@
 // (registers prefetched one slice ahead) and applies the causal frontier per row.  Online softmax
 // in the exp2 domain, fp32 statistics and accumulation, mma.sync m16n8k16 (legacy tensor path).
 #include "paged_attention.cuh"
+#include "prefix_prefill.cuh"
+#include "prefix_prefill_umma.cuh"
 
 #include <atomic>
 
 namespace b200 {
-
-struct PrefixParams {
-  const void *q, *k, *v;
-  void* out;
-  const void *k_cache, *v_cache;
-  const int32_t *block_tables, *start_loc, *seq_lens, *ctx_lens;
-  const float* alibi_slopes;
-  const unsigned char* kv_scratch;  // new k/v pre-staged as pages (prefix_stage_kv_kernel) or NULL
-  int num_heads, num_kv_heads, group, max_blocks_per_seq, sliding_window, tok_tile, num_stages,
-      stage_shift;
-  int64_t scratch_slices;  // capacity of kv_scratch in (slice, all kv heads) units: staged indices are guarded
-  int64_t q_s0, q_s1, k_s0, k_s1, v_s0, v_s1, o_s0, o_s1, kc_bs, kc_hs, vc_bs, vc_hs;
-  float scale_log2;
-};
 
 constexpr int kPrefixWarps = 4;
 
@@ -615,8 +603,64 @@ constexpr size_t prefix_smem(int ns) {
   return (size_t)ns * 2 * D * BS * 2 + (size_t)ns * 16 + 1024;
 }
 
+// The staging pre-pass shared by both tile loops: packed new k/v -> page layout in the scratch.
 template <typename T, int D, int BS>
-int launch_prefix(PrefixParams& p, int num_seqs, int max_query_len, int device, cudaStream_t stream) {
+int launch_prefix_stage(const PrefixParams& p, int num_seqs, int max_query_len, cudaStream_t stream) {
+  dim3 sgrid((max_query_len + BS - 1) / BS, p.num_kv_heads, num_seqs);
+  prefix_stage_kv_kernel<T, D, BS><<<sgrid, 128, 0, stream>>>(p, const_cast<unsigned char*>(p.kv_scratch));
+  count_launch();
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+// Can the tcgen05 tile loop (prefix_prefill_umma.cuh) serve this call?  Head 128, no ALiBi / window,
+// staged new tokens, 16-byte aligned q / out rows, a GQA group that fits one 128-row M tile.
+template <int D>
+bool umma_eligible(const PrefixParams& p) {
+  auto a16 = [](const void* ptr) { return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0; };
+  return D == 128 && p.alibi_slopes == nullptr && p.sliding_window == 0 && p.kv_scratch != nullptr &&
+         p.group <= 128 && a16(p.q) && a16(p.out) && p.q_s0 % 8 == 0 && p.q_s1 % 8 == 0 && p.o_s0 % 8 == 0 &&
+         p.o_s1 % 8 == 0;
+}
+
+template <typename T, int BS>
+int launch_prefix_umma(PrefixParams& p, int num_seqs, int max_query_len, int device, cudaStream_t stream) {
+  p.tok_tile = kUmmaRows / p.group;
+  auto kern = context_attention_umma_kernel<T, BS>;
+  static std::atomic<int> configured[64];
+  const int slot = device & 63;
+  if (!configured[slot].load(std::memory_order_acquire)) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUmmaSmem));
+    configured[slot].store(1, std::memory_order_release);
+  }
+  const int rc = launch_prefix_stage<T, 128, BS>(p, num_seqs, max_query_len, stream);
+  if (rc != B200_OK) return rc;
+  const int tiles = (max_query_len + p.tok_tile - 1) / p.tok_tile;
+  B200_CHECK_ARG(p.num_kv_heads <= 65535 && num_seqs <= 65535, "context_attention_fwd: grid too large");
+  dim3 grid(tiles, p.num_kv_heads, num_seqs);
+  kern<<<grid, kUmmaThreads, kUmmaSmem, stream>>>(p);
+  count_launch();
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+template <typename T, int D, int BS>
+int launch_prefix(PrefixParams& p, int num_seqs, int max_query_len, int device, cudaStream_t stream, int path) {
+  if constexpr (D == 128) {
+    const bool can = umma_eligible<D>(p);
+    if (path == B200_PREFIX_PATH_TCGEN05 && !can) {
+      set_error("context_attention_fwd: the tcgen05 path needs head size 128, no ALiBi / sliding window, "
+                "a staging scratch and 16-byte aligned q / out rows");
+      return B200_ERR_UNSUPPORTED;
+    }
+    // auto: the 256-row tile pays once a sequence brings at least one full M tile of rows
+    if (can && (path == B200_PREFIX_PATH_TCGEN05 ||
+                (path == B200_PREFIX_PATH_AUTO && (int64_t)max_query_len * p.group >= 128)))
+      return launch_prefix_umma<T, BS>(p, num_seqs, max_query_len, device, stream);
+  } else if (path == B200_PREFIX_PATH_TCGEN05) {
+    set_error("context_attention_fwd: the tcgen05 path needs head size 128 (got %d)", D);
+    return B200_ERR_UNSUPPORTED;
+  }
   constexpr int GROWS = D <= 128 ? 16 : 8;
   constexpr int ROWS = kPrefixWarps * GROWS;
   B200_CHECK_ARG(p.group <= ROWS, "context_attention_fwd: %d q-heads per kv-head exceed the %d-row tile",
@@ -637,10 +681,8 @@ int launch_prefix(PrefixParams& p, int num_seqs, int max_query_len, int device, 
     configured[plain][slot].store(1, std::memory_order_release);
   }
   if (p.kv_scratch != nullptr) {
-    dim3 sgrid((max_query_len + BS - 1) / BS, p.num_kv_heads, num_seqs);
-    prefix_stage_kv_kernel<T, D, BS><<<sgrid, 128, 0, stream>>>(p, const_cast<unsigned char*>(p.kv_scratch));
-    count_launch();
-    B200_CUDA_OK(cudaGetLastError());
+    const int rc = launch_prefix_stage<T, D, BS>(p, num_seqs, max_query_len, stream);
+    if (rc != B200_OK) return rc;
   }
   const int tiles = (max_query_len + p.tok_tile - 1) / p.tok_tile;
   B200_CHECK_ARG(p.num_kv_heads <= 65535 && num_seqs <= 65535, "context_attention_fwd: grid too large");
@@ -655,9 +697,10 @@ int launch_prefix(PrefixParams& p, int num_seqs, int max_query_len, int device, 
 
 template <typename T>
 int dispatch_prefix(PrefixParams& p, int head_size, int block_size, int num_seqs, int max_query_len,
-                    int device, cudaStream_t stream) {
+                    int device, cudaStream_t stream, int path) {
 #define B200_PFX(DD, BB) \
-  if (head_size == DD && block_size == BB) return launch_prefix<T, DD, BB>(p, num_seqs, max_query_len, device, stream);
+  if (head_size == DD && block_size == BB) \
+    return launch_prefix<T, DD, BB>(p, num_seqs, max_query_len, device, stream, path);
 #ifdef B200_FAST_BUILD
   B200_PFX(64, 16) B200_PFX(128, 16)
 #else
@@ -686,7 +729,7 @@ extern "C" int64_t b200_context_attention_scratch_bytes(int64_t num_tokens, int 
   return (num_tokens / block_size + num_seqs + 1) * (int64_t)num_kv_heads * 2 * head_size * block_size * 2;
 }
 
-extern "C" int b200_context_attention_fwd(
+extern "C" int b200_context_attention_fwd_path(
     const void* q, const void* k, const void* v, void* out, const void* key_cache,
     const void* value_cache, const int32_t* block_tables, const int32_t* start_loc,
     const int32_t* seq_lens, const int32_t* ctx_lens, int num_seqs, int num_heads, int num_kv_heads,
@@ -695,7 +738,10 @@ extern "C" int b200_context_attention_fwd(
     int64_t o_stride0, int64_t o_stride1, int64_t kc_block_stride, int64_t kc_head_stride,
     int64_t vc_block_stride, int64_t vc_head_stride, const float* alibi_slopes, int sliding_window,
     float scale, void* kv_scratch, int64_t kv_scratch_bytes, int64_t num_tokens, int dtype,
-    int device, b200_stream_t stream) {
+    int device, b200_stream_t stream, int path) {
+  B200_CHECK_ARG(path == B200_PREFIX_PATH_AUTO || path == B200_PREFIX_PATH_MMA_SYNC ||
+                     path == B200_PREFIX_PATH_TCGEN05,
+                 "context_attention_fwd: unknown path %d", path);
   B200_CHECK_ARG(num_seqs >= 0 && max_query_len >= 0 && head_size > 0 && block_size > 0,
                  "context_attention_fwd: bad sizes");
   if (num_seqs == 0 || max_query_len == 0) return B200_OK;
@@ -739,6 +785,10 @@ extern "C" int b200_context_attention_fwd(
                      ? static_cast<const unsigned char*>(kv_scratch)
                      : nullptr;
   p.scratch_slices = p.kv_scratch ? kv_scratch_bytes / ((int64_t)num_kv_heads * 2 * head_size * block_size * 2) : 0;
+  if (dtype == B200_DT_F32 && path == B200_PREFIX_PATH_TCGEN05) {
+    set_error("context_attention_fwd: the tcgen05 path runs fp16 / bf16 only");
+    return B200_ERR_UNSUPPORTED;
+  }
   if (dtype == B200_DT_F32) {
     B200_CHECK_ARG(head_size % 4 == 0 && head_size <= 256 && (reinterpret_cast<uintptr_t>(q) & 15) == 0 &&
                        q_stride0 % 4 == 0 && q_stride1 % 4 == 0,
@@ -752,6 +802,26 @@ extern "C" int b200_context_attention_fwd(
     return B200_OK;
   }
   if (dtype == B200_DT_F16)
-    return dispatch_prefix<__half>(p, head_size, block_size, num_seqs, max_query_len, dev, (cudaStream_t)stream);
-  return dispatch_prefix<__nv_bfloat16>(p, head_size, block_size, num_seqs, max_query_len, dev, (cudaStream_t)stream);
+    return dispatch_prefix<__half>(p, head_size, block_size, num_seqs, max_query_len, dev, (cudaStream_t)stream,
+                                   path);
+  return dispatch_prefix<__nv_bfloat16>(p, head_size, block_size, num_seqs, max_query_len, dev,
+                                        (cudaStream_t)stream, path);
+}
+
+extern "C" int b200_context_attention_fwd(
+    const void* q, const void* k, const void* v, void* out, const void* key_cache,
+    const void* value_cache, const int32_t* block_tables, const int32_t* start_loc,
+    const int32_t* seq_lens, const int32_t* ctx_lens, int num_seqs, int num_heads, int num_kv_heads,
+    int head_size, int block_size, int max_blocks_per_seq, int max_query_len, int64_t q_stride0,
+    int64_t q_stride1, int64_t k_stride0, int64_t k_stride1, int64_t v_stride0, int64_t v_stride1,
+    int64_t o_stride0, int64_t o_stride1, int64_t kc_block_stride, int64_t kc_head_stride,
+    int64_t vc_block_stride, int64_t vc_head_stride, const float* alibi_slopes, int sliding_window,
+    float scale, void* kv_scratch, int64_t kv_scratch_bytes, int64_t num_tokens, int dtype,
+    int device, b200_stream_t stream) {
+  return b200_context_attention_fwd_path(
+      q, k, v, out, key_cache, value_cache, block_tables, start_loc, seq_lens, ctx_lens, num_seqs, num_heads,
+      num_kv_heads, head_size, block_size, max_blocks_per_seq, max_query_len, q_stride0, q_stride1, k_stride0,
+      k_stride1, v_stride0, v_stride1, o_stride0, o_stride1, kc_block_stride, kc_head_stride, vc_block_stride,
+      vc_head_stride, alibi_slopes, sliding_window, scale, kv_scratch, kv_scratch_bytes, num_tokens, dtype,
+      device, stream, B200_PREFIX_PATH_AUTO);
 }
