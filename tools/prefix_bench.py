@@ -4,8 +4,7 @@
 Workload (defaults): Llama-3-8B-shaped bf16 (32 q / 8 kv heads, head 128, block 16), B sequences
 with `ctx` cached tokens each and `qlen` new tokens.  Reports device time (CUDA events), attention
 TFLOP/s = 4*D*H*sum(qlen*ctx + qlen*(qlen+1)/2) / time, the fraction of the measured dense bf16
-peak (MEASURED_PEAKS.json; the kernel runs on the legacy mma.sync path, so this fraction is an upper
-bound on nothing -- it shows the distance to the tcgen05 roofline), and the same call served by
+peak (MEASURED_PEAKS.json), for the tile loop picked with --path, and the same call served by
 torch SDPA on a gathered contiguous copy of the context (a library baseline on the same box; the
 gather is excluded from its time).  Prints one JSON line.
 """
@@ -37,6 +36,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--dtype", default="bfloat16")
     ap.add_argument("--no-scratch", action="store_true", help="CTA-local staging of the new k/v")
+    ap.add_argument("--path", default="auto", choices=["auto", "mma_sync", "tcgen05"],
+                    help="tile loop: library choice, the mma.sync kernel, or the tcgen05 / TMEM kernel")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     dtype = getattr(torch, a.dtype)
@@ -59,7 +60,7 @@ def main():
 
     def ours():
         context_attention_fwd(q, k, v, out, kc, vc, bt, start[:-1], seq, cl, ql, None, None,
-                              use_scratch=not a.no_scratch)
+                              use_scratch=not a.no_scratch, path=a.path)
 
     # library baseline: contiguous K/V per sequence (context gathered from the pages + new tokens)
     nctx = (ctx + BS - 1) // BS
@@ -103,7 +104,7 @@ def main():
         "roofline": {"bound": "tensor", "achieved": round(tf, 1), "peak": peak, "unit": "TFLOP/s",
                      "frac": round(tf / peak, 4),
                      "peak_source": "MEASURED_PEAKS.json bf16_tflops" if peaks else "datasheet",
-                     "note": "mma.sync path; tcgen05 is the next step for this row"},
+                     "path": a.path},
         "kv_bytes_algorithmic": kv_bytes, "kv_GBps_algorithmic": round(kv_bytes / ms / 1e6, 1),
         "sdpa_library_ms": round(ms_sdpa, 4), "speedup_vs_sdpa": round(ms_sdpa / ms, 3),
         "max_abs_vs_sdpa": err, "gpu_launches": int(launches), "steps": a.steps, "warmup": a.warmup,
