@@ -23,7 +23,10 @@
 //                     128x128x16) and O_w += P_w V (TS form), and signals mbarriers with tcgen05.commit.
 //
 // TMEM (512 columns): S_0 | S_1 | O_0 | O_1, 128 fp32 columns each; P_w aliases the first 64 of S_w.
-// Shared memory: Q 2 x 32 KiB, two K/V stages of 64 KiB, all in 64-element-of-K slabs of 128-byte rows.
+// Shared memory: Q 2 x 32 KiB, a ring of three K tiles and a ring of two V tiles (32 KiB each), all in
+// 64-element-of-K slabs of 128-byte rows.  The MMA thread runs one step ahead on the S side:
+// P.V_w(j) is followed at once by S_w(j+1) = Q_w K(j+1)^T, so softmax_w(j+1) overlaps the other
+// M tile's P.V -- the two warpgroups ping-pong on the tensor pipe and on the MUFU pipe.
 #pragma once
 
 #include <type_traits>
@@ -37,7 +40,8 @@ constexpr int kUmmaThreads = 512;
 constexpr int kUmmaRows = 256;         // rows per CTA (two M tiles)
 constexpr int kUmmaKeys = 128;         // keys per K/V tile
 constexpr uint32_t kUmmaTile = 32768;  // bytes of one 128 x 128 16-bit operand tile
-constexpr uint32_t kUmmaSmem = 2 * kUmmaTile + 2 * 2 * kUmmaTile + 128 + 1024;
+constexpr int kUmmaKStages = 3, kUmmaVStages = 2;
+constexpr uint32_t kUmmaSmem = (2 + kUmmaKStages + kUmmaVStages) * kUmmaTile + 128 + 1024;
 
 template <typename T, int BS>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
@@ -76,13 +80,19 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   const int nt = n_ctx_tiles + last_tok / kUmmaKeys + 1;
 
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t q_s = base, kv_s = base + 2 * kUmmaTile, bars = kv_s + 4 * kUmmaTile;
-  const uint32_t kv_full = bars, kv_empty = bars + 16, s_full = bars + 32, p_full = bars + 48, slot = bars + 64;
+  const uint32_t q_s = base, k_ring = base + 2 * kUmmaTile, v_ring = k_ring + kUmmaKStages * kUmmaTile,
+                 bars = v_ring + kUmmaVStages * kUmmaTile;
+  const uint32_t k_full = bars, k_empty = bars + 24, v_full = bars + 48, v_empty = bars + 64, s_full = bars + 80,
+                 p_full = bars + 96, slot = bars + 112;
 
   if (tid == 0) {
+    for (int i = 0; i < kUmmaKStages; ++i) {
+      mbar_init(k_full + 8 * i, 128);
+      mbar_init(k_empty + 8 * i, 1);
+    }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(kv_full + 8 * i, 128);
-      mbar_init(kv_empty + 8 * i, 1);
+      mbar_init(v_full + 8 * i, 128);
+      mbar_init(v_empty + 8 * i, 1);
       mbar_init(s_full + 8 * i, 1);
       mbar_init(p_full + 8 * i, 128);
     }
@@ -255,10 +265,8 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
     const uint32_t k_off = (uint32_t)(8 * gidx + l8) * 128u;  // K row of this thread's key
     const uint32_t v_off =
         (uint32_t)(gidx >> 3) * 16384u + (uint32_t)l8 * 128u + (uint32_t)(((gidx & 7) ^ l8) << 4);
+    int ks = 0, kround = 0;  // K ring position of tile j, number of times the ring wrapped
     for (int j = 0; j < nt; ++j) {
-      const int st = j & 1;
-      if (j >= 2) mbar_wait_wd(kv_empty + 8 * st, (uint32_t)(((j >> 1) - 1) & 1));
-      const uint32_t k_t = kv_s + (uint32_t)st * 2 * kUmmaTile, v_t = k_t + kUmmaTile;
       const bool is_ctx = j < n_ctx_tiles;
       const int pos = kUmmaKeys * (is_ctx ? j : j - n_ctx_tiles) + 8 * gidx;  // first key of the group
       const int nval = min(8, max(0, (is_ctx ? ctx : qlen) - pos));           // its valid keys
@@ -275,80 +283,113 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
         }
       }
       {
+        if (kround > 0) mbar_wait_wd(k_empty + 8 * ks, (uint32_t)((kround - 1) & 1));
         const unsigned char* src = kpage + (toff + l8) * 16;
         const uint32_t nb = l8 < nval ? 16u : 0u;
-        const uint32_t dst = k_t + k_off;
+        const uint32_t dst = k_ring + (uint32_t)ks * kUmmaTile + k_off;
 #pragma unroll
         for (int c = 0; c < 16; ++c)
           cp_async16(dst + (uint32_t)(c >> 3) * 16384u + (uint32_t)(((c & 7) ^ l8) << 4), src + c * BS * 16, nb);
-      }
-      {
-        const unsigned char* src = vpage + toff * 2 + l8 * BS * 2;
-        const uint32_t nb = nval > 0 ? 16u : 0u;
-        const uint32_t dst = v_t + v_off;
-#pragma unroll
-        for (int i = 0; i < 16; ++i) cp_async16(dst + (uint32_t)i * 1024u, src + i * 8 * BS * 2, nb);
-      }
-      cp_async_commit();
-      cp_async_wait_all();
-      if (is_ctx && nval > 0 && nval < 8) {
-        // last context page: slots past ctx_len may hold anything (NaN included); P is 0 there, but
-        // 0 * NaN is not -- clear them in the V tile (staged new-token pages are already zero filled)
-        uint32_t mk[4];
-#pragma unroll
-        for (int wd = 0; wd < 4; ++wd)
-          mk[wd] = (2 * wd < nval ? 0x0000ffffu : 0u) | (2 * wd + 1 < nval ? 0xffff0000u : 0u);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const uint32_t a = v_t + v_off + (uint32_t)i * 1024u;
-          uint32_t x, y, z, u;
-          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(u) : "r"(a));
-          x &= mk[0];
-          y &= mk[1];
-          z &= mk[2];
-          u &= mk[3];
-          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(u)
-                       : "memory");
+        cp_async_arrive_noinc(k_full + 8 * ks);
+        if (++ks == kUmmaKStages) {
+          ks = 0;
+          ++kround;
         }
       }
-      fence_proxy_async_smem();
-      mbar_arrive(kv_full + 8 * st);
+      {
+        const int vs = j & 1;
+        if (j >= 2) mbar_wait_wd(v_empty + 8 * vs, (uint32_t)(((j >> 1) - 1) & 1));
+        const unsigned char* src = vpage + toff * 2 + l8 * BS * 2;
+        const uint32_t nb = nval > 0 ? 16u : 0u;
+        const uint32_t dst = v_ring + (uint32_t)vs * kUmmaTile + v_off;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) cp_async16(dst + (uint32_t)i * 1024u, src + i * 8 * BS * 2, nb);
+        if (is_ctx && nval > 0 && nval < 8) {
+          // last context page: slots past ctx_len may hold anything (NaN included); P is 0 there, but
+          // 0 * NaN is not -- clear them in the V tile (staged new-token pages are already zero filled)
+          cp_async_commit();
+          cp_async_wait_all();
+          uint32_t mk[4];
+#pragma unroll
+          for (int wd = 0; wd < 4; ++wd)
+            mk[wd] = (2 * wd < nval ? 0x0000ffffu : 0u) | (2 * wd + 1 < nval ? 0xffff0000u : 0u);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const uint32_t a = dst + (uint32_t)i * 1024u;
+            uint32_t x, y, z, u;
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(u) : "r"(a));
+            x &= mk[0];
+            y &= mk[1];
+            z &= mk[2];
+            u &= mk[3];
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(u)
+                         : "memory");
+          }
+          fence_proxy_async_smem();
+          mbar_arrive(v_full + 8 * vs);
+        } else {
+          cp_async_arrive_noinc(v_full + 8 * vs);
+        }
+      }
     }
+    cp_async_commit();
+    cp_async_wait_all();  // nothing of this thread is still in flight when the CTA winds down
   } else if (warp == 12) {
     // ======================= MMA issuer =======================
     constexpr uint32_t idesc = idesc_f16(FMT, 128, 128);
-    for (int j = 0; j < nt; ++j) {
-      const int st = j & 1;
-      mbar_wait_wd(kv_full + 8 * st, (uint32_t)((j >> 1) & 1));
-      fence_after_sync();
-      const uint32_t k_t = kv_s + (uint32_t)st * 2 * kUmmaTile, v_t = k_t + kUmmaTile;
-      if (lane == 0) {
-        const uint64_t db = sw128_desc(k_t);
-        for (int w = 0; w < nq; ++w) {
-          const uint64_t da = sw128_desc(q_s + (uint32_t)w * kUmmaTile);
+    // S_w = Q_w K(tile in ring slot ks)^T, then "S_w ready"
+    auto issue_qk = [&](int w, int ks) {
+      const uint64_t da = sw128_desc(q_s + (uint32_t)w * kUmmaTile);
+      const uint64_t db = sw128_desc(k_ring + (uint32_t)ks * kUmmaTile);
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk) {
-            const uint32_t adv = (uint32_t)(kk >> 2) * 16384u + (uint32_t)(kk & 3) * 32u;
-            mma_ss(tmem + (uint32_t)w * 128u, desc_advance(da, adv), desc_advance(db, adv), idesc, kk > 0);
-          }
-          commit(s_full + 8 * w);
-        }
+      for (int kk = 0; kk < 8; ++kk) {
+        const uint32_t adv = (uint32_t)(kk >> 2) * 16384u + (uint32_t)(kk & 3) * 32u;
+        mma_ss(tmem + (uint32_t)w * 128u, desc_advance(da, adv), desc_advance(db, adv), idesc, kk > 0);
       }
-      __syncwarp();
+      commit(s_full + 8 * w);
+    };
+    // the gather wrote the tiles through the generic proxy: order those writes (acquired through the
+    // mbarrier) before this thread's async-proxy reads
+    mbar_wait_wd(k_full, 0u);
+    fence_proxy_async_smem();
+    fence_after_sync();
+    if (lane == 0) {
+      for (int w = 0; w < nq; ++w) issue_qk(w, 0);
+      commit(k_empty);
+    }
+    __syncwarp();
+    int ks = 1 % kUmmaKStages, kround = 0;  // ring position of tile j + 1
+    for (int j = 0; j < nt; ++j) {
+      const int vs = j & 1;
+      mbar_wait_wd(v_full + 8 * vs, (uint32_t)((j >> 1) & 1));
+      fence_proxy_async_smem();
+      const bool more = j + 1 < nt;
       for (int w = 0; w < nq; ++w) {
         mbar_wait_wd(p_full + 8 * w, (uint32_t)(j & 1));
+        if (more && w == 0) {
+          mbar_wait_wd(k_full + 8 * ks, (uint32_t)(kround & 1));
+          fence_proxy_async_smem();
+        }
         fence_after_sync();
         if (lane == 0) {
-          const uint64_t db = sw128_desc(v_t);
+          const uint64_t db = sw128_desc(v_ring + (uint32_t)vs * kUmmaTile);
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk) {
             const uint32_t adv = (uint32_t)(kk >> 2) * 16384u + (uint32_t)(kk & 3) * 32u;
             mma_ts(tmem + 256u + (uint32_t)w * 128u, tmem + (uint32_t)w * 128u + (uint32_t)kk * 8u,
                    desc_advance(db, adv), idesc, (j > 0 || kk > 0) ? 1u : 0u);
           }
-          if (w == nq - 1) commit(kv_empty + 8 * st);
+          if (w == nq - 1) commit(v_empty + 8 * vs);
+          if (more) {
+            issue_qk(w, ks);  // overwrites P_w(j): ordered behind P.V_w(j) in the tensor pipe
+            if (w == nq - 1) commit(k_empty + 8 * ks);
+          }
         }
         __syncwarp();
+      }
+      if (++ks == kUmmaKStages) {
+        ks = 0;
+        ++kround;
       }
     }
     if (lane == 0)

@@ -115,6 +115,11 @@ __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void* src, u
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src), "r"(src_bytes)
                : "memory");
 }
+// mbarrier arrive (already counted in the barrier's expected arrivals: .noinc) that fires once every
+// cp.async this thread issued so far has landed -- the producer never blocks on its own copies
+__device__ __forceinline__ void cp_async_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
