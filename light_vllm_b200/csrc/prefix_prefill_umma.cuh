@@ -4,7 +4,8 @@
 // fp16 / bf16, no ALiBi, no sliding window.  Everything else stays on prefix_prefill.cu.
 //
 // One CTA (16 warps, one per SM) owns (sequence, KV head, tile of 256 / G query tokens): its 256 rows
-// (query token, q-head of the GQA group) are two 128-row M tiles that share every K/V tile.
+// (query token, q-head of the GQA group) are two 128-row M tiles that share every K/V tile.  Keys are
+// consumed in steps of 64.
 //
 //   warps 0-3 / 4-7   softmax warpgroup of M tile 0 / 1: one thread per row (= TMEM lane).  S comes back
 //                     with tcgen05.ld, the row maximum needs no shuffle, P = exp2(S*c - m) is written
@@ -15,18 +16,23 @@
 //   warps 8-11        gather: the cache keeps a K page as [D/8][BS][8] and a V page as [D][BS]; neither is
 //                     an operand layout tcgen05.mma can address across pages.  Both ARE permutations of
 //                     16-byte chunks of the K-major SWIZZLE_128B operand tiles, so 128 threads move a
-//                     128-key K tile and V tile with 32 cp.async (LDGSTS, 16 B) each -- one block-table
+//                     64-key K tile and V tile with 16 cp.async (LDGSTS, 16 B) each -- one block-table
 //                     lookup per thread and tile, global reads in 128..512-byte runs, bank-conflict-free
-//                     shared-memory writes, no register staging, no extra pass over HBM.  New tokens
-//                     arrive as pages too (prefix_stage_kv_kernel), so there is one gather path.
-//   warp 12           one elected thread issues every tcgen05.mma: S_w = Q_w K^T (SS form, 8 k-steps of
-//                     128x128x16) and O_w += P_w V (TS form), and signals mbarriers with tcgen05.commit.
+//                     shared-memory writes, no register staging, no extra pass over HBM; completion is
+//                     signalled by cp.async.mbarrier.arrive, so the gather never blocks on its own
+//                     copies.  New tokens arrive as pages too (prefix_stage_kv_kernel): one gather path.
+//   warp 12           one elected thread issues every tcgen05.mma: S_w = Q_w K^T (SS form, 128x64x16) and
+//                     O_w += P_w V (TS form, 128x128x16), and signals mbarriers with tcgen05.commit.
 //
-// TMEM (512 columns): S_0 | S_1 | O_0 | O_1, 128 fp32 columns each; P_w aliases the first 64 of S_w.
-// Shared memory: Q 2 x 32 KiB, a ring of three K tiles and a ring of two V tiles (32 KiB each), all in
-// 64-element-of-K slabs of 128-byte rows.  The MMA thread runs one step ahead on the S side:
-// P.V_w(j) is followed at once by S_w(j+1) = Q_w K(j+1)^T, so softmax_w(j+1) overlaps the other
-// M tile's P.V -- the two warpgroups ping-pong on the tensor pipe and on the MUFU pipe.
+// The softmax of an M tile must never wait for the tensor pipe: S_w is double buffered in TMEM and the
+// MMA thread runs TWO steps ahead on the S side -- P.V_w(j) is followed at once by S_w(j+2) into the
+// buffer P_w(j) just vacated -- so S_w(j+1) is already complete when softmax_w(j) ends.  The
+// exponentials (MUFU, 16 / clock / SM: as many cycles per step as the two MMAs) are then the only
+// serial resource of a warpgroup, and the two warpgroups share it back to back.
+//
+// TMEM (512 columns): S_0a S_0b S_1a S_1b (64 fp32 columns each) | O_0 | O_1 (128 each); P aliases the
+// first 32 columns of its S buffer.  Shared memory: Q 2 x 32 KiB, rings of K tiles and V tiles
+// (16 KiB each), all in 64-element-of-K slabs of 128-byte rows.
 #pragma once
 
 #include <type_traits>
@@ -37,17 +43,20 @@
 namespace b200 {
 
 constexpr int kUmmaThreads = 512;
-constexpr int kUmmaRows = 256;         // rows per CTA (two M tiles)
-constexpr int kUmmaKeys = 128;         // keys per K/V tile
-constexpr uint32_t kUmmaTile = 32768;  // bytes of one 128 x 128 16-bit operand tile
-constexpr int kUmmaKStages = 3, kUmmaVStages = 2;
-constexpr uint32_t kUmmaSmem = (2 + kUmmaKStages + kUmmaVStages) * kUmmaTile + 128 + 1024;
+constexpr int kUmmaRows = 256;          // rows per CTA (two M tiles)
+constexpr int kUmmaKeys = 64;           // keys per step
+constexpr uint32_t kUmmaQTile = 32768;  // bytes of one 128-row x 128-d Q tile
+constexpr uint32_t kUmmaKVTile = 16384; // bytes of one 64-key K (or V) tile
+constexpr int kUmmaKStages = 5, kUmmaVStages = 4;
+constexpr uint32_t kUmmaBarBytes = 8 * (2 * kUmmaKStages + 2 * kUmmaVStages + 4 + 4 + 2) + 16;
+constexpr uint32_t kUmmaSmem = 2 * kUmmaQTile + (kUmmaKStages + kUmmaVStages) * kUmmaKVTile + kUmmaBarBytes + 1024;
 
 template <typename T, int BS>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
 context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   using namespace umma;
   constexpr int D = 128;
+  constexpr int KT = kUmmaKeys;
   constexpr int PAGE_BYTES = D * BS * 2;
   constexpr int SLICE_BYTES = 2 * PAGE_BYTES;
   constexpr int FMT = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
@@ -61,6 +70,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   const int ctx = p.ctx_lens[seq];
   const int qlen = p.seq_lens[seq] - ctx;
   const int G = p.group;
+  const int dbg = p.stage_shift;  // timing experiments only (B200_UMMA_DEBUG): results are wrong when set
   const int m0 = (int)(gridDim.x - 1 - blockIdx.x) * p.tok_tile;  // heaviest (latest) query tiles first
   if (m0 >= qlen) return;
   const int64_t start = p.start_loc[seq];
@@ -75,27 +85,31 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   }
   const int rows_valid = tile_tokens * G;
   const int nq = rows_valid > 128 ? 2 : 1;  // M tiles that hold at least one real row
-  const int n_ctx_tiles = (ctx + kUmmaKeys - 1) / kUmmaKeys;
+  const int n_ctx_tiles = (ctx + KT - 1) / KT;
   const int last_tok = m0 + tile_tokens - 1;
-  const int nt = n_ctx_tiles + last_tok / kUmmaKeys + 1;
+  const int nt = n_ctx_tiles + last_tok / KT + 1;
 
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t q_s = base, k_ring = base + 2 * kUmmaTile, v_ring = k_ring + kUmmaKStages * kUmmaTile,
-                 bars = v_ring + kUmmaVStages * kUmmaTile;
-  const uint32_t k_full = bars, k_empty = bars + 24, v_full = bars + 48, v_empty = bars + 64, s_full = bars + 80,
-                 p_full = bars + 96, slot = bars + 112;
+  const uint32_t q_s = base, k_ring = base + 2 * kUmmaQTile, v_ring = k_ring + kUmmaKStages * kUmmaKVTile,
+                 bars = v_ring + kUmmaVStages * kUmmaKVTile;
+  const uint32_t k_full = bars, k_empty = k_full + 8 * kUmmaKStages, v_full = k_empty + 8 * kUmmaKStages,
+                 v_empty = v_full + 8 * kUmmaVStages, s_full = v_empty + 8 * kUmmaVStages,  // [w][buffer]
+                 p_full = s_full + 32, o_ready = p_full + 32, slot = o_ready + 16;  // p_full: [w][buffer]
 
   if (tid == 0) {
     for (int i = 0; i < kUmmaKStages; ++i) {
       mbar_init(k_full + 8 * i, 128);
       mbar_init(k_empty + 8 * i, 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kUmmaVStages; ++i) {
       mbar_init(v_full + 8 * i, 128);
       mbar_init(v_empty + 8 * i, 1);
+    }
+    for (int i = 0; i < 4; ++i) {
       mbar_init(s_full + 8 * i, 1);
       mbar_init(p_full + 8 * i, 128);
     }
+    for (int i = 0; i < 2; ++i) mbar_init(o_ready + 8 * i, 1);
     mbar_fence_init();
   }
   if (warp == 0) tmem_alloc(slot, 512);
@@ -112,7 +126,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
         const int head = kvh * G + R % G;
         const T* src = qg + (start + m0 + ti) * p.q_s0 + (int64_t)head * p.q_s1 + c * 8;
         const int r = R & 127;
-        cp_async16(q_s + (uint32_t)(R >> 7) * kUmmaTile + (uint32_t)(c >> 3) * 16384u + sw128_offset(r, c & 7),
+        cp_async16(q_s + (uint32_t)(R >> 7) * kUmmaQTile + (uint32_t)(c >> 3) * 16384u + sw128_offset(r, c & 7),
                    src, 16);
       }
     }
@@ -127,9 +141,9 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(slot));
 
   if (warp < 8) {
-    setmaxnreg_inc<200>();
+    setmaxnreg_inc<192>();
   } else {
-    setmaxnreg_dec<56>();
+    setmaxnreg_dec<64>();
   }
 
   if (warp < 8) {
@@ -147,28 +161,29 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
       const float c2 = p.scale_log2;
       float m_ref = kNInf, l = 0.f;
       for (int j = 0; j < nt; ++j) {
-        mbar_wait_wd(s_full + 8 * w, (uint32_t)(j & 1));
+        const int b = j & 1;
+        mbar_wait_wd(s_full + 8 * (2 * w + b), (uint32_t)((j >> 1) & 1));
         fence_after_sync();
-        uint32_t s[4][32];
-#pragma unroll
-        for (int c = 0; c < 4; ++c) tmem_ld32(t_s + 32 * c, s[c]);
+        uint32_t s[2][32];
+        tmem_ld32(t_s + 64 * b, s[0]);
+        tmem_ld32(t_s + 64 * b + 32, s[1]);
         tmem_wait_ld();
         // visible keys of this row in the tile: a prefix [0, lim)
         int lim;
         if (j < n_ctx_tiles)
-          lim = min(kUmmaKeys, ctx - kUmmaKeys * j);
+          lim = min(KT, ctx - KT * j);
         else
-          lim = min(kUmmaKeys, max(0, iq - kUmmaKeys * (j - n_ctx_tiles) + 1));
-        if (__any_sync(FULL, lim < kUmmaKeys)) {
+          lim = min(KT, max(0, iq - KT * (j - n_ctx_tiles) + 1));
+        if (__any_sync(FULL, lim < KT)) {
 #pragma unroll
-          for (int c = 0; c < 4; ++c)
+          for (int c = 0; c < 2; ++c)
 #pragma unroll
             for (int i = 0; i < 32; ++i)
               if (32 * c + i >= lim) s[c][i] = __float_as_uint(kNInf);
         }
         float mx0 = kNInf, mx1 = kNInf, mx2 = kNInf, mx3 = kNInf;
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
+        for (int c = 0; c < 2; ++c)
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
             mx0 = fmaxf(mx0, __uint_as_float(s[c][i]));
@@ -189,6 +204,9 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
           resc = true;
         }
         if (j > 0 && __any_sync(FULL, resc)) {
+          // O_w must hold every product up to step j - 1 before it is scaled
+          mbar_wait_wd(o_ready + 8 * w, (uint32_t)((j - 1) & 1));
+          fence_after_sync();
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
             uint32_t o[32];
@@ -201,35 +219,39 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
         }
         const float neg_m = m_ref == kNInf ? 0.f : -m_ref;
         float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+        uint32_t pk[32];
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint32_t pk[32];
+        for (int c = 0; c < 2; ++c) {
 #pragma unroll
-          for (int cc = 0; cc < 2; ++cc) {
-            const int c = 2 * h + cc;
-#pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-              const float e0 = fast_exp2(fmaf(__uint_as_float(s[c][i]), c2, neg_m));
-              const float e1 = fast_exp2(fmaf(__uint_as_float(s[c][i + 1]), c2, neg_m));
-              const float e2 = fast_exp2(fmaf(__uint_as_float(s[c][i + 2]), c2, neg_m));
-              const float e3 = fast_exp2(fmaf(__uint_as_float(s[c][i + 3]), c2, neg_m));
-              l0 += e0;
-              l1 += e1;
-              l2 += e2;
-              l3 += e3;
-              pk[16 * cc + i / 2] = MmaOp<T>::pack(e0, e1);
-              pk[16 * cc + i / 2 + 1] = MmaOp<T>::pack(e2, e3);
+          for (int i = 0; i < 32; i += 4) {
+            float e0 = fmaf(__uint_as_float(s[c][i]), c2, neg_m), e1 = fmaf(__uint_as_float(s[c][i + 1]), c2, neg_m);
+            float e2 = fmaf(__uint_as_float(s[c][i + 2]), c2, neg_m), e3 = fmaf(__uint_as_float(s[c][i + 3]), c2, neg_m);
+            if (!(dbg & 1)) {
+              e0 = fast_exp2(e0);
+              e1 = fast_exp2(e1);
+              e2 = fast_exp2(e2);
+              e3 = fast_exp2(e3);
             }
+            l0 += e0;
+            l1 += e1;
+            l2 += e2;
+            l3 += e3;
+            pk[16 * c + i / 2] = MmaOp<T>::pack(e0, e1);
+            pk[16 * c + i / 2 + 1] = MmaOp<T>::pack(e2, e3);
           }
-          tmem_st32(t_s + 32 * h, pk);  // P over the first 64 columns of S (all of S is in registers)
         }
+        tmem_st32(t_s + 64 * b, pk);  // P over the first 32 columns of this S buffer (S is in registers)
         l += (l0 + l1) + (l2 + l3);
         tmem_wait_st();
         fence_before_sync();
-        mbar_arrive(p_full + 8 * w);
+        // per S buffer: the softmax may finish step j + 1 before the MMA thread has looked at step j
+        mbar_arrive(p_full + 8 * (2 * w + b));
       }
       // ---- epilogue: O / l -> out ----
-      mbar_wait_wd(s_full + 8 * w, (uint32_t)(nt & 1));
+      // o_ready has completed nt - 2 phases for certain (S(nt-1) was issued behind P.V(nt-3)); walk the
+      // last two one by one -- a parity wait can only tell "this phase" from "the next"
+      if (nt >= 2) mbar_wait_wd(o_ready + 8 * w, (uint32_t)((nt - 2) & 1));
+      mbar_wait_wd(o_ready + 8 * w, (uint32_t)((nt - 1) & 1));
       fence_after_sync();
       const float inv = l > 0.f ? 1.f / l : 0.f;
       T* orow = static_cast<T*>(p.out) + (start + m0 + min(ti, tile_tokens - 1)) * p.o_s0 +
@@ -254,22 +276,24 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
     }
   } else if (warp < 12) {
     // ======================= gather warps: pages -> swizzled operand tiles =======================
+    // 16 groups of 8 threads: group g serves the 8 keys [8 (g & 7), +8) of the tile; for K it moves the
+    // d chunks [8 (g >> 3), +8) of its key (lane = key), for V the rows d = 64 (g >> 3) + 8 i + lane of
+    // its 8-key chunk.  Every thread therefore touches one page per tile.
     const int pt = tid - 256;
-    const int gidx = pt >> 3, l8 = pt & 7;  // group of 8 keys inside the tile, lane inside the group
+    const int g = pt >> 3, l8 = pt & 7, kg = g & 7, hi = g >> 3;
     const unsigned char* kbase = static_cast<const unsigned char*>(p.k_cache) + (int64_t)kvh * p.kc_hs * 2;
     const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (int64_t)kvh * p.vc_hs * 2;
     const int32_t* bt = p.block_tables + (int64_t)seq * p.max_blocks_per_seq;
     const unsigned char* sbase =
         p.kv_scratch + (((int64_t)(start / BS) + seq) * p.num_kv_heads + kvh) * SLICE_BYTES;
     const int64_t slice_stride = (int64_t)p.num_kv_heads * SLICE_BYTES;
-    const uint32_t k_off = (uint32_t)(8 * gidx + l8) * 128u;  // K row of this thread's key
-    const uint32_t v_off =
-        (uint32_t)(gidx >> 3) * 16384u + (uint32_t)l8 * 128u + (uint32_t)(((gidx & 7) ^ l8) << 4);
-    int ks = 0, kround = 0;  // K ring position of tile j, number of times the ring wrapped
+    const uint32_t k_off = (uint32_t)hi * 8192u + (uint32_t)(8 * kg + l8) * 128u;
+    const uint32_t v_off = (uint32_t)(64 * hi + l8) * 128u + (uint32_t)((kg ^ l8) << 4);
+    int ks = 0, kround = 0, vs = 0, vround = 0;  // ring positions of tile j, times each ring wrapped
     for (int j = 0; j < nt; ++j) {
       const bool is_ctx = j < n_ctx_tiles;
-      const int pos = kUmmaKeys * (is_ctx ? j : j - n_ctx_tiles) + 8 * gidx;  // first key of the group
-      const int nval = min(8, max(0, (is_ctx ? ctx : qlen) - pos));           // its valid keys
+      const int pos = KT * (is_ctx ? j : j - n_ctx_tiles) + 8 * kg;  // first key of the group
+      const int nval = min(8, max(0, (is_ctx ? ctx : qlen) - pos));  // its valid keys
       const int toff = pos % BS;
       const unsigned char *kpage = kbase, *vpage = vbase;
       if (nval > 0) {
@@ -284,12 +308,11 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
       }
       {
         if (kround > 0) mbar_wait_wd(k_empty + 8 * ks, (uint32_t)((kround - 1) & 1));
-        const unsigned char* src = kpage + (toff + l8) * 16;
+        const unsigned char* src = kpage + (toff + l8) * 16 + hi * 8 * BS * 16;
         const uint32_t nb = l8 < nval ? 16u : 0u;
-        const uint32_t dst = k_ring + (uint32_t)ks * kUmmaTile + k_off;
+        const uint32_t dst = k_ring + (uint32_t)ks * kUmmaKVTile + k_off;
 #pragma unroll
-        for (int c = 0; c < 16; ++c)
-          cp_async16(dst + (uint32_t)(c >> 3) * 16384u + (uint32_t)(((c & 7) ^ l8) << 4), src + c * BS * 16, nb);
+        for (int i = 0; i < 8; ++i) cp_async16(dst + (uint32_t)((i ^ l8) << 4), src + i * BS * 16, (dbg & 4) ? 0u : nb);
         cp_async_arrive_noinc(k_full + 8 * ks);
         if (++ks == kUmmaKStages) {
           ks = 0;
@@ -297,13 +320,12 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
         }
       }
       {
-        const int vs = j & 1;
-        if (j >= 2) mbar_wait_wd(v_empty + 8 * vs, (uint32_t)(((j >> 1) - 1) & 1));
-        const unsigned char* src = vpage + toff * 2 + l8 * BS * 2;
+        if (vround > 0) mbar_wait_wd(v_empty + 8 * vs, (uint32_t)((vround - 1) & 1));
+        const unsigned char* src = vpage + toff * 2 + (64 * hi + l8) * BS * 2;
         const uint32_t nb = nval > 0 ? 16u : 0u;
-        const uint32_t dst = v_ring + (uint32_t)vs * kUmmaTile + v_off;
+        const uint32_t dst = v_ring + (uint32_t)vs * kUmmaKVTile + v_off;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) cp_async16(dst + (uint32_t)i * 1024u, src + i * 8 * BS * 2, nb);
+        for (int i = 0; i < 8; ++i) cp_async16(dst + (uint32_t)i * 1024u, src + i * 8 * BS * 2, (dbg & 4) ? 0u : nb);
         if (is_ctx && nval > 0 && nval < 8) {
           // last context page: slots past ctx_len may hold anything (NaN included); P is 0 there, but
           // 0 * NaN is not -- clear them in the V tile (staged new-token pages are already zero filled)
@@ -314,7 +336,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
           for (int wd = 0; wd < 4; ++wd)
             mk[wd] = (2 * wd < nval ? 0x0000ffffu : 0u) | (2 * wd + 1 < nval ? 0xffff0000u : 0u);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
+          for (int i = 0; i < 8; ++i) {
             const uint32_t a = dst + (uint32_t)i * 1024u;
             uint32_t x, y, z, u;
             asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(u) : "r"(a));
@@ -330,71 +352,84 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
         } else {
           cp_async_arrive_noinc(v_full + 8 * vs);
         }
+        if (++vs == kUmmaVStages) {
+          vs = 0;
+          ++vround;
+        }
       }
     }
     cp_async_commit();
     cp_async_wait_all();  // nothing of this thread is still in flight when the CTA winds down
   } else if (warp == 12) {
     // ======================= MMA issuer =======================
-    constexpr uint32_t idesc = idesc_f16(FMT, 128, 128);
-    // S_w = Q_w K(tile in ring slot ks)^T, then "S_w ready"
-    auto issue_qk = [&](int w, int ks) {
-      const uint64_t da = sw128_desc(q_s + (uint32_t)w * kUmmaTile);
-      const uint64_t db = sw128_desc(k_ring + (uint32_t)ks * kUmmaTile);
+    constexpr uint32_t idesc_s = idesc_f16(FMT, 128, KT);
+    constexpr uint32_t idesc_o = idesc_f16(FMT, 128, 128);
+    // S_w(step in K ring slot ks) = Q_w K^T into S buffer b, then "S_w[b] ready"
+    auto issue_qk = [&](int w, int b, int ks) {
+      const uint64_t da = sw128_desc(q_s + (uint32_t)w * kUmmaQTile);
+      const uint64_t db = sw128_desc(k_ring + (uint32_t)ks * kUmmaKVTile);
+      if (!(dbg & 8))
 #pragma unroll
       for (int kk = 0; kk < 8; ++kk) {
-        const uint32_t adv = (uint32_t)(kk >> 2) * 16384u + (uint32_t)(kk & 3) * 32u;
-        mma_ss(tmem + (uint32_t)w * 128u, desc_advance(da, adv), desc_advance(db, adv), idesc, kk > 0);
+        const uint32_t in_slab = (uint32_t)(kk & 3) * 32u;
+        mma_ss(tmem + (uint32_t)w * 128u + (uint32_t)b * 64u, desc_advance(da, (uint32_t)(kk >> 2) * 16384u + in_slab),
+               desc_advance(db, (uint32_t)(kk >> 2) * 8192u + in_slab), idesc_s, kk > 0);
       }
-      commit(s_full + 8 * w);
+      commit(s_full + 8 * (2 * w + b));
     };
-    // the gather wrote the tiles through the generic proxy: order those writes (acquired through the
-    // mbarrier) before this thread's async-proxy reads
-    mbar_wait_wd(k_full, 0u);
-    fence_proxy_async_smem();
-    fence_after_sync();
-    if (lane == 0) {
-      for (int w = 0; w < nq; ++w) issue_qk(w, 0);
-      commit(k_empty);
-    }
-    __syncwarp();
-    int ks = 1 % kUmmaKStages, kround = 0;  // ring position of tile j + 1
-    for (int j = 0; j < nt; ++j) {
-      const int vs = j & 1;
-      mbar_wait_wd(v_full + 8 * vs, (uint32_t)((j >> 1) & 1));
+    // Prologue: S(0) and S(1).  The gather wrote the tiles through the generic proxy: order those writes
+    // (acquired through the mbarrier) before this thread's async-proxy reads.
+    int ks = 0, kround = 0;  // K ring position of the next step whose S has not been issued
+    const int pre = min(2, nt);
+    for (int jj = 0; jj < pre; ++jj) {
+      mbar_wait_wd(k_full + 8 * ks, 0u);
       fence_proxy_async_smem();
-      const bool more = j + 1 < nt;
+      fence_after_sync();
+      if (elect_one()) {
+        for (int w = 0; w < nq; ++w) issue_qk(w, jj, ks);
+        commit(k_empty + 8 * ks);
+      }
+      __syncwarp();
+      ++ks;
+    }
+    int vs = 0, vround = 0;
+    for (int j = 0; j < nt; ++j) {
+      mbar_wait_wd(v_full + 8 * vs, (uint32_t)(vround & 1));
+      fence_proxy_async_smem();
+      const bool more = j + 2 < nt;
       for (int w = 0; w < nq; ++w) {
-        mbar_wait_wd(p_full + 8 * w, (uint32_t)(j & 1));
+        mbar_wait_wd(p_full + 8 * (2 * w + (j & 1)), (uint32_t)((j >> 1) & 1));
         if (more && w == 0) {
           mbar_wait_wd(k_full + 8 * ks, (uint32_t)(kround & 1));
           fence_proxy_async_smem();
         }
         fence_after_sync();
-        if (lane == 0) {
-          const uint64_t db = sw128_desc(v_ring + (uint32_t)vs * kUmmaTile);
+        if (elect_one()) {
+          const uint64_t db = sw128_desc(v_ring + (uint32_t)vs * kUmmaKVTile);
+          const uint32_t t_p = tmem + (uint32_t)w * 128u + (uint32_t)(j & 1) * 64u;
+          if (!(dbg & 2))
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk) {
-            const uint32_t adv = (uint32_t)(kk >> 2) * 16384u + (uint32_t)(kk & 3) * 32u;
-            mma_ts(tmem + 256u + (uint32_t)w * 128u, tmem + (uint32_t)w * 128u + (uint32_t)kk * 8u,
-                   desc_advance(db, adv), idesc, (j > 0 || kk > 0) ? 1u : 0u);
-          }
+          for (int kk = 0; kk < KT / 16; ++kk)
+            mma_ts(tmem + 256u + (uint32_t)w * 128u, t_p + (uint32_t)kk * 8u, desc_advance(db, (uint32_t)kk * 32u),
+                   idesc_o, (j > 0 || kk > 0) ? 1u : 0u);
+          commit(o_ready + 8 * w);
           if (w == nq - 1) commit(v_empty + 8 * vs);
           if (more) {
-            issue_qk(w, ks);  // overwrites P_w(j): ordered behind P.V_w(j) in the tensor pipe
+            issue_qk(w, j & 1, ks);  // overwrites P_w(j): ordered behind P.V_w(j) in the tensor pipe
             if (w == nq - 1) commit(k_empty + 8 * ks);
           }
         }
         __syncwarp();
       }
-      if (++ks == kUmmaKStages) {
+      if (more && ++ks == kUmmaKStages) {
         ks = 0;
         ++kround;
       }
+      if (++vs == kUmmaVStages) {
+        vs = 0;
+        ++vround;
+      }
     }
-    if (lane == 0)
-      for (int w = 0; w < nq; ++w) commit(s_full + 8 * w);  // "O_w is final" (tracks every MMA above)
-    __syncwarp();
   }
 
   fence_before_sync();
