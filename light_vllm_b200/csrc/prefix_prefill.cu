@@ -18,7 +18,6 @@
 #include "prefix_prefill_umma.cuh"
 
 #include <atomic>
-#include <cstdlib>
 
 namespace b200 {
 
@@ -627,10 +626,6 @@ bool umma_eligible(const PrefixParams& p) {
 template <typename T, int BS>
 int launch_prefix_umma(PrefixParams& p, int num_seqs, int max_query_len, int device, cudaStream_t stream) {
   p.tok_tile = kUmmaRows / p.group;
-  {
-    const char* e = getenv("B200_UMMA_DEBUG");  // timing experiments only
-    p.stage_shift = e ? atoi(e) : 0;
-  }
   auto kern = context_attention_umma_kernel<T, BS>;
   static std::atomic<int> configured[64];
   const int slot = device & 63;

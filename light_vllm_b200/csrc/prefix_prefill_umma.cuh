@@ -21,8 +21,10 @@
 //                     shared-memory writes, no register staging, no extra pass over HBM; completion is
 //                     signalled by cp.async.mbarrier.arrive, so the gather never blocks on its own
 //                     copies.  New tokens arrive as pages too (prefix_stage_kv_kernel): one gather path.
-//   warp 12           one elected thread issues every tcgen05.mma: S_w = Q_w K^T (SS form, 128x64x16) and
-//                     O_w += P_w V (TS form, 128x128x16), and signals mbarriers with tcgen05.commit.
+//   warps 12 / 13     one elected thread per M tile issues its tcgen05.mma stream: S_w = Q_w K^T (SS form,
+//                     128x64x16) and O_w += P_w V (TS form, 128x128x16), and signals mbarriers with
+//                     tcgen05.commit.  Issue sits under elect.sync so that ptxas keeps descriptors in
+//                     uniform registers (a lane == 0 branch costs a uniform-loop per instruction).
 //
 // The softmax of an M tile must never wait for the tensor pipe: S_w is double buffered in TMEM and the
 // MMA thread runs TWO steps ahead on the S side -- P.V_w(j) is followed at once by S_w(j+2) into the
@@ -70,7 +72,6 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   const int ctx = p.ctx_lens[seq];
   const int qlen = p.seq_lens[seq] - ctx;
   const int G = p.group;
-  const int dbg = p.stage_shift;  // timing experiments only (B200_UMMA_DEBUG): results are wrong when set
   const int m0 = (int)(gridDim.x - 1 - blockIdx.x) * p.tok_tile;  // heaviest (latest) query tiles first
   if (m0 >= qlen) return;
   const int64_t start = p.start_loc[seq];
@@ -99,11 +100,11 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   if (tid == 0) {
     for (int i = 0; i < kUmmaKStages; ++i) {
       mbar_init(k_full + 8 * i, 128);
-      mbar_init(k_empty + 8 * i, 1);
+      mbar_init(k_empty + 8 * i, nq);
     }
     for (int i = 0; i < kUmmaVStages; ++i) {
       mbar_init(v_full + 8 * i, 128);
-      mbar_init(v_empty + 8 * i, 1);
+      mbar_init(v_empty + 8 * i, nq);
     }
     for (int i = 0; i < 4; ++i) {
       mbar_init(s_full + 8 * i, 1);
@@ -224,14 +225,10 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
         for (int c = 0; c < 2; ++c) {
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
-            float e0 = fmaf(__uint_as_float(s[c][i]), c2, neg_m), e1 = fmaf(__uint_as_float(s[c][i + 1]), c2, neg_m);
-            float e2 = fmaf(__uint_as_float(s[c][i + 2]), c2, neg_m), e3 = fmaf(__uint_as_float(s[c][i + 3]), c2, neg_m);
-            if (!(dbg & 1)) {
-              e0 = fast_exp2(e0);
-              e1 = fast_exp2(e1);
-              e2 = fast_exp2(e2);
-              e3 = fast_exp2(e3);
-            }
+            const float e0 = fast_exp2(fmaf(__uint_as_float(s[c][i]), c2, neg_m));
+            const float e1 = fast_exp2(fmaf(__uint_as_float(s[c][i + 1]), c2, neg_m));
+            const float e2 = fast_exp2(fmaf(__uint_as_float(s[c][i + 2]), c2, neg_m));
+            const float e3 = fast_exp2(fmaf(__uint_as_float(s[c][i + 3]), c2, neg_m));
             l0 += e0;
             l1 += e1;
             l2 += e2;
@@ -312,7 +309,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
         const uint32_t nb = l8 < nval ? 16u : 0u;
         const uint32_t dst = k_ring + (uint32_t)ks * kUmmaKVTile + k_off;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) cp_async16(dst + (uint32_t)((i ^ l8) << 4), src + i * BS * 16, (dbg & 4) ? 0u : nb);
+        for (int i = 0; i < 8; ++i) cp_async16(dst + (uint32_t)((i ^ l8) << 4), src + i * BS * 16, nb);
         cp_async_arrive_noinc(k_full + 8 * ks);
         if (++ks == kUmmaKStages) {
           ks = 0;
@@ -325,7 +322,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
         const uint32_t nb = nval > 0 ? 16u : 0u;
         const uint32_t dst = v_ring + (uint32_t)vs * kUmmaKVTile + v_off;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) cp_async16(dst + (uint32_t)i * 1024u, src + i * 8 * BS * 2, (dbg & 4) ? 0u : nb);
+        for (int i = 0; i < 8; ++i) cp_async16(dst + (uint32_t)i * 1024u, src + i * 8 * BS * 2, nb);
         if (is_ctx && nval > 0 && nval < 8) {
           // last context page: slots past ctx_len may hold anything (NaN included); P is 0 there, but
           // 0 * NaN is not -- clear them in the V tile (staged new-token pages are already zero filled)
@@ -360,22 +357,27 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
     }
     cp_async_commit();
     cp_async_wait_all();  // nothing of this thread is still in flight when the CTA winds down
-  } else if (warp == 12) {
-    // ======================= MMA issuer =======================
+  } else if (warp < 12 + nq) {
+    // ======================= MMA issuers: warp 12 for M tile 0, warp 13 for M tile 1 =======================
+    // Two independent instruction streams (disjoint TMEM, shared read-only K/V tiles): while one thread
+    // polls its barriers the other one's MMAs keep the tensor pipe fed.  A K/V ring slot is free once
+    // BOTH have committed past it (empty barriers count nq arrivals).
+    const int w = warp - 12;
     constexpr uint32_t idesc_s = idesc_f16(FMT, 128, KT);
     constexpr uint32_t idesc_o = idesc_f16(FMT, 128, 128);
-    // S_w(step in K ring slot ks) = Q_w K^T into S buffer b, then "S_w[b] ready"
-    auto issue_qk = [&](int w, int b, int ks) {
-      const uint64_t da = sw128_desc(q_s + (uint32_t)w * kUmmaQTile);
+    const uint32_t t_sw = tmem + (uint32_t)w * 128u, t_ow = tmem + 256u + (uint32_t)w * 128u;
+    const uint64_t da = sw128_desc(q_s + (uint32_t)w * kUmmaQTile);
+    // S_w(step in K ring slot ks) = Q_w K^T into S buffer b, then "S_w[b] ready" and "done with the slot"
+    auto issue_qk = [&](int b, int ks) {
       const uint64_t db = sw128_desc(k_ring + (uint32_t)ks * kUmmaKVTile);
-      if (!(dbg & 8))
 #pragma unroll
       for (int kk = 0; kk < 8; ++kk) {
         const uint32_t in_slab = (uint32_t)(kk & 3) * 32u;
-        mma_ss(tmem + (uint32_t)w * 128u + (uint32_t)b * 64u, desc_advance(da, (uint32_t)(kk >> 2) * 16384u + in_slab),
+        mma_ss(t_sw + (uint32_t)b * 64u, desc_advance(da, (uint32_t)(kk >> 2) * 16384u + in_slab),
                desc_advance(db, (uint32_t)(kk >> 2) * 8192u + in_slab), idesc_s, kk > 0);
       }
       commit(s_full + 8 * (2 * w + b));
+      commit(k_empty + 8 * ks);
     };
     // Prologue: S(0) and S(1).  The gather wrote the tiles through the generic proxy: order those writes
     // (acquired through the mbarrier) before this thread's async-proxy reads.
@@ -385,42 +387,30 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
       mbar_wait_wd(k_full + 8 * ks, 0u);
       fence_proxy_async_smem();
       fence_after_sync();
-      if (elect_one()) {
-        for (int w = 0; w < nq; ++w) issue_qk(w, jj, ks);
-        commit(k_empty + 8 * ks);
-      }
+      if (elect_one()) issue_qk(jj, ks);
       __syncwarp();
       ++ks;
     }
     int vs = 0, vround = 0;
     for (int j = 0; j < nt; ++j) {
-      mbar_wait_wd(v_full + 8 * vs, (uint32_t)(vround & 1));
-      fence_proxy_async_smem();
       const bool more = j + 2 < nt;
-      for (int w = 0; w < nq; ++w) {
-        mbar_wait_wd(p_full + 8 * (2 * w + (j & 1)), (uint32_t)((j >> 1) & 1));
-        if (more && w == 0) {
-          mbar_wait_wd(k_full + 8 * ks, (uint32_t)(kround & 1));
-          fence_proxy_async_smem();
-        }
-        fence_after_sync();
-        if (elect_one()) {
-          const uint64_t db = sw128_desc(v_ring + (uint32_t)vs * kUmmaKVTile);
-          const uint32_t t_p = tmem + (uint32_t)w * 128u + (uint32_t)(j & 1) * 64u;
-          if (!(dbg & 2))
+      mbar_wait_wd(p_full + 8 * (2 * w + (j & 1)), (uint32_t)((j >> 1) & 1));
+      mbar_wait_wd(v_full + 8 * vs, (uint32_t)(vround & 1));
+      if (more) mbar_wait_wd(k_full + 8 * ks, (uint32_t)(kround & 1));
+      fence_proxy_async_smem();
+      fence_after_sync();
+      if (elect_one()) {
+        const uint64_t db = sw128_desc(v_ring + (uint32_t)vs * kUmmaKVTile);
+        const uint32_t t_p = t_sw + (uint32_t)(j & 1) * 64u;
 #pragma unroll
-          for (int kk = 0; kk < KT / 16; ++kk)
-            mma_ts(tmem + 256u + (uint32_t)w * 128u, t_p + (uint32_t)kk * 8u, desc_advance(db, (uint32_t)kk * 32u),
-                   idesc_o, (j > 0 || kk > 0) ? 1u : 0u);
-          commit(o_ready + 8 * w);
-          if (w == nq - 1) commit(v_empty + 8 * vs);
-          if (more) {
-            issue_qk(w, j & 1, ks);  // overwrites P_w(j): ordered behind P.V_w(j) in the tensor pipe
-            if (w == nq - 1) commit(k_empty + 8 * ks);
-          }
-        }
-        __syncwarp();
+        for (int kk = 0; kk < KT / 16; ++kk)
+          mma_ts(t_ow, t_p + (uint32_t)kk * 8u, desc_advance(db, (uint32_t)kk * 32u), idesc_o,
+                 (j > 0 || kk > 0) ? 1u : 0u);
+        commit(o_ready + 8 * w);
+        commit(v_empty + 8 * vs);
+        if (more) issue_qk(j & 1, ks);  // overwrites P_w(j): ordered behind P.V_w(j) in the tensor pipe
       }
+      __syncwarp();
       if (more && ++ks == kUmmaKStages) {
         ks = 0;
         ++kround;
