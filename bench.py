@@ -72,6 +72,163 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_peak_tflops():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["bf16_tflops"]), "MEASURED_PEAKS.json bf16_tflops (burst: kernel timed alone)"
+    except Exception:
+        return 1590.0, "fallback (B200_PROFILING.md)"
+
+
+def prefix_prefill_record(dev, steps):
+    """SURVEY 8f rank 4 on the driver-run line: context_attention_fwd (prefix / chunked prefill over the
+    paged cache) at 16 sequences x (4096 cached + 512 new tokens), Llama-3-8B-shaped bf16 -- the tcgen05 /
+    TMEM tile loop against the round-1 mma.sync tile loop of the same library, CUDA events, inputs
+    (300 MB of K/V) larger than L2.  Parity: both tile loops against each other on the timed shape and
+    against the CPU oracle on a small ragged case (the one place outside cpu_baseline where this file
+    executes oracle/, as the checker)."""
+    import torch
+    from light_vllm_b200.attention.prefix_prefill import context_attention_fwd
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    from make_golden_prefix import make_prefix_case
+    from oracle import oracle
+
+    B, ctx, ql, H, KH, D, BS = 16, 4096, 512, 32, 8, 128, 16
+    dtype = torch.bfloat16
+    g = torch.Generator(device=dev).manual_seed(3)
+
+    def rnd(*shape):
+        return ((torch.rand(*shape, device=dev, generator=g) - 0.5) * 0.5).to(dtype)
+
+    T = B * ql
+    q, k, v = rnd(T, H, D), rnd(T, KH, D), rnd(T, KH, D)
+    nblk = (ctx + ql + BS - 1) // BS
+    NB = B * nblk + 4
+    kc, vc = rnd(NB, KH, D // 8, BS, 8), rnd(NB, KH, D, BS)
+    bt = torch.randperm(NB, generator=torch.Generator().manual_seed(1))[:B * nblk].int().view(B, nblk).to(dev)
+    start = torch.arange(0, T + 1, ql, dtype=torch.int32, device=dev)
+    seq = torch.full((B,), ctx + ql, dtype=torch.int32, device=dev)
+    cl = torch.full((B,), ctx, dtype=torch.int32, device=dev)
+    outs = {}
+    ms = {}
+    for path in ("tcgen05", "mma_sync"):
+        out = torch.empty_like(q)
+
+        def call():
+            context_attention_fwd(q, k, v, out, kc, vc, bt, start[:-1], seq, cl, ql, None, None, path=path)
+
+        for _ in range(3):
+            call()
+        torch.cuda.synchronize()
+        n = max(5, steps if path == "tcgen05" else steps // 2)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            call()
+        e1.record()
+        torch.cuda.synchronize()
+        ms[path] = e0.elapsed_time(e1) / n
+        outs[path] = out
+    cross = (outs["tcgen05"].float() - outs["mma_sync"].float()).abs().max().item()
+    # oracle check on a small ragged case (seconds of scalar C)
+    c = make_prefix_case([0, 77, 300], [130, 64, 257], 8, 2, D, BS, dtype, seed=5)
+    d = {n: (t.to(dev) if isinstance(t, torch.Tensor) else t) for n, t in c.items()}
+    got = torch.empty_like(d["query"])
+    context_attention_fwd(d["query"], d["key"], d["value"], got, d["key_cache"], d["value_cache"],
+                          d["block_tables"], d["query_start_loc"][:-1], d["seq_lens"], d["context_lens"],
+                          c["max_query_len"], None, None, path="tcgen05")
+    want = torch.zeros_like(c["query"])
+    oracle.context_attention_fwd(c["query"], c["key"], c["value"], want, c["key_cache"], c["value_cache"],
+                                 c["block_tables"], c["query_start_loc"][:-1], c["seq_lens"],
+                                 c["context_lens"], c["max_query_len"], None, None)
+    err = (got.float().cpu() - want.float()).abs().max().item()
+    flops = 4.0 * D * H * B * (ql * ctx + ql * (ql + 1) / 2)
+    peak, src = measured_peak_tflops()
+    tf = flops / ms["tcgen05"] / 1e9
+    if err > 1e-2 or cross > 1e-2:
+        raise RuntimeError(f"prefix prefill parity failed: oracle {err}, tile loops {cross}")
+    return {"workload": f"{B} seqs x ({ctx} cached + {ql} new tokens), bf16 H{H}/KH{KH}/D{D}/BS{BS}",
+            "kernel": "context_attention_umma_kernel (tcgen05.mma, TMEM accumulators)",
+            "ms_per_call": round(ms["tcgen05"], 4), "TFLOPs": round(tf, 1),
+            "roofline": {"bound": "tensor", "achieved": round(tf, 1), "peak": peak, "unit": "TFLOP/s",
+                         "frac": round(tf / peak, 4), "peak_source": src},
+            "mma_sync_ms_per_call": round(ms["mma_sync"], 4),
+            "speedup_vs_mma_sync": round(ms["mma_sync"] / ms["tcgen05"], 3),
+            "parity": {"max_abs_vs_oracle_small_case": err, "max_abs_tcgen05_vs_mma_sync": cross, "tol": 1e-2}}
+
+
+def other_config_record(name, dev, steps):
+    """One more BASELINE.json config on the driver-run line: the attention launch alone at the config's
+    full shape (one pool, larger than L2, cycled halves are not needed: a pool is >= 4 GiB), CUDA events."""
+    import torch
+    from light_vllm_b200 import _custom_ops as ops
+    from light_vllm_b200 import _lib
+    from light_vllm_b200.attention import PagedAttention, PagedB200AttentionBackend
+
+    c = CONFIGS[name]
+    dtype = getattr(torch, c["dtype"])
+    kv = c["kv"]
+    H, KH, D, BS, B, ctx = c["H"], c["KH"], c["D"], c["BS"], c["B"], c["ctx"]
+    scale = D ** -0.5
+    k_scale = v_scale = 1.0 if kv == "auto" else 0.05
+    bps = (ctx + BS - 1) // BS
+    NB = B * bps + 64
+    shape = PagedB200AttentionBackend.get_kv_cache_shape(NB, BS, KH, D)
+    if kv == "auto":
+        pool = torch.empty(shape, dtype=dtype, device=dev).uniform_(-scale, scale)
+    else:
+        pool = torch.empty(shape, dtype=torch.uint8, device=dev)
+        half = NB // 2  # convert in two halves: the 16-bit source of a whole pool would double the footprint
+        for lo, hi in ((0, half), (half, NB)):
+            src = torch.empty((2, hi - lo) + tuple(shape[2:]), dtype=dtype, device=dev).uniform_(-scale, scale)
+            for t in range(2):
+                ops.convert_fp8(pool[t, lo:hi], src[t], k_scale, "fp8")
+            del src
+    kc, vc = PagedAttention.split_kv_cache(pool, KH, D)
+    bt = torch.randperm(NB - 64)[:B * bps].view(B, bps).int().to(dev)
+    sl = torch.full((B,), ctx, dtype=torch.int32, device=dev)
+    q = torch.empty(B, H, D, dtype=dtype, device=dev).uniform_(-scale, scale)
+    out = torch.empty_like(q)
+    P = (ctx + 511) // 512
+    scratch = (torch.empty(B, H, P, dtype=torch.float32, device=dev),
+               torch.empty(B, H, P, dtype=torch.float32, device=dev),
+               torch.empty(B, H, P, D, dtype=dtype, device=dev))
+
+    def call():
+        if c["version"] == 1:
+            ops.paged_attention_v1(out, q, kc, vc, KH, scale, bt, sl, BS, ctx, None, kv, k_scale, v_scale,
+                                   0, 0, 0, 64, 0)
+        else:
+            ops.paged_attention_v2(out, *scratch, q, kc, vc, KH, scale, bt, sl, BS, ctx, None, kv, k_scale,
+                                   v_scale, 0, 0, 0, 64, 0)
+
+    for _ in range(3):
+        call()
+    torch.cuda.synchronize()
+    n = max(5, steps // 2)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        call()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n
+    if not torch.isfinite(out.float()).all():
+        raise RuntimeError(f"{name}: non-finite attention output")
+    peak, src = measured_peak_gbs()
+    alg = algorithmic_bytes_attention(c)
+    gbs = alg / ms / 1e6
+    del pool, kc, vc, scratch
+    torch.cuda.empty_cache()
+    return {"workload": c["label"], "kv_cache_dtype": kv, "us_per_launch": round(ms * 1e3, 1),
+            "algorithmic_bytes": alg, "decode_tokens_per_s_per_layer": round(B / ms * 1e3, 1),
+            "roofline": {"bound": "hbm", "achieved": round(gbs, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(gbs / peak, 4), "peak_source": src},
+            "l2": f"one {alg >> 20} MiB pass per launch, far larger than L2",
+            "plan": _lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, dev.index or 0)}
+
+
 def ncu_traffic(config_name):
     """dram__bytes_read.sum + dram__bytes_write.sum of one attention launch, from the committed
     `ncu --set full` capture of this config (profiles/ncu_traffic.json); None if never captured."""
@@ -604,14 +761,31 @@ def run_b200_arm(args, c):
     if preempt:
         pre = preemption_exercise(args, c, dev, pools, block_tables_h, NB, device_step, timed)
 
+    extra = {}
+    if world == 1 and rank == 0 and not args.no_extra_records and args.config == "c2":
+        del graph
+        pools.clear()
+        split.clear()
+        torch.cuda.empty_cache()
+        for name, fn in (("prefix_prefill", lambda: prefix_prefill_record(dev, args.steps)),
+                         ("c3", lambda: other_config_record("c3", dev, args.steps)),
+                         ("c4", lambda: other_config_record("c4", dev, args.steps))):
+            try:
+                extra[name] = fn()
+            except Exception as e:  # reported beside the headline, never allowed to take it down
+                extra[name] = {"error": repr(e)}
+            torch.cuda.empty_cache()
+
     ctx_shard = None
     if world > 1 and not args.no_ctx_shard:
-        del pools, split, graph
+        del graph
+        pools.clear()
+        split.clear()
         torch.cuda.empty_cache()
         ctx_shard = ctx_shard_record(dev, rank, world, dist, max(10, args.steps))
 
     return dict(rank=rank, world=world, ms_total=ms_total, ms_e2e=ms_e2e, ms_e2e_eager=ms_e2e_eager,
-                ms_attn=ms_attn, parity=parity, reference_cuda=ref_cuda, ctx_shard=ctx_shard,
+                ms_attn=ms_attn, parity=parity, reference_cuda=ref_cuda, ctx_shard=ctx_shard, extra=extra,
                 clocks=clocks, launches=launches, h2d=h2d, d2h=d2h, L=L, preemption=pre,
                 plan=_lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, local_rank),
                 dist=dist if world > 1 else None)
@@ -724,6 +898,8 @@ def main():
     ap.add_argument("--no-preempt", action="store_true", help="c5: skip the preemption exercise")
     ap.add_argument("--no-reference-cuda", action="store_true",
                     help="skip the (untimed-region) leg that times the reference's CUDA kernels")
+    ap.add_argument("--no-extra-records", action="store_true",
+                    help="N = 1, c2: skip the prefix_prefill / c3 / c4 records printed beside the headline")
     ap.add_argument("--no-ctx-shard", action="store_true",
                     help="--gpus N >= 2: skip the context-sharded decode record")
     args = ap.parse_args()
@@ -793,6 +969,10 @@ def main():
             line["reference_cuda"] = r["reference_cuda"]
         if r.get("ctx_shard") is not None:
             line["ctx_shard"] = r["ctx_shard"]
+        if r.get("extra"):
+            if "prefix_prefill" in r["extra"]:
+                line["prefix_prefill"] = r["extra"]["prefix_prefill"]
+            line["other_configs"] = {k: v for k, v in r["extra"].items() if k != "prefix_prefill"}
         if cpu is not None and "error" not in cpu:
             # same statistic as the --impl reference arm: MEAN over the timed steps (>= 3 untimed)
             gbs = cpu["kv_bytes"] / cpu["mean_s"] / 1e9
