@@ -343,8 +343,10 @@ typedef struct {
 typedef struct {
   int32_t num_warps;   /* warps per CTA (1..8)                                              */
   int32_t num_stages;  /* K+V page pairs in flight per warp                                 */
-  int32_t split;       /* v1: cluster size (context split through DSMEM); v2: partition     */
-                       /* length in units of 512 tokens                                     */
+  int32_t split;       /* v1: cluster size (context split through DSMEM); v2: partitions    */
+                       /* per sequence at max_seq_len (each >= 512 tokens, balanced pages)  */
+  int32_t head_rows;   /* q-heads of a GQA group per CTA (1..group; fewer than the group =   */
+                       /* several CTAs share each KV page through L2: small-batch grids)     */
 } b200_attn_tuning_t;
 int b200_paged_attention_plan(int version, int num_seqs, int num_heads, int num_kv_heads,
                               int head_size, int block_size, int max_seq_len, int q_dtype,

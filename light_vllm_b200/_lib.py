@@ -68,7 +68,7 @@ class AttnPlan(ctypes.Structure):
 
 class AttnTuning(ctypes.Structure):
     """Mirror of ``b200_attn_tuning_t`` (per-call launch overrides; 0 = library default)."""
-    _fields_ = [(n, ctypes.c_int32) for n in ("num_warps", "num_stages", "split")]
+    _fields_ = [(n, ctypes.c_int32) for n in ("num_warps", "num_stages", "split", "head_rows")]
 
 
 def _load():
@@ -135,14 +135,14 @@ _DT = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
 def _tuning(tuning):
     if tuning is None:
         return None
-    w, s, c = tuning
-    return ctypes.byref(AttnTuning(int(w), int(s), int(c)))
+    w, s, c, *rest = tuning
+    return ctypes.byref(AttnTuning(int(w), int(s), int(c), int(rest[0]) if rest else 0))
 
 
 def attention_plan(version, num_seqs, num_heads, num_kv_heads, head_size, block_size, max_seq_len,
                    dtype, kv_cache_dtype="auto", device=0, tuning=None) -> dict:
     """Launch geometry the library would pick (needs a CUDA device).  ``tuning`` = optional
-    (warps, stages, split) per-call override, as ``paged_attention_tuned`` takes."""
+    (warps, stages, split[, head_rows]) per-call override, as ``paged_attention_tuned`` takes."""
     plan = AttnPlan()
     kv = lib.b200_parse_kv_cache_dtype(kv_cache_dtype.encode())
     rc = lib.b200_paged_attention_plan(version, num_seqs, num_heads, num_kv_heads, head_size,

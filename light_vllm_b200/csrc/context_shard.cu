@@ -56,6 +56,9 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
                           long long timeout_cycles) {
   extern __shared__ float wsm[];  // [4 warps][head_size] partial folds
   __shared__ uint32_t epoch_s;
+  // Launched with programmatic stream serialisation: this grid may be scheduled while the partition pass
+  // drains; nothing of its output is read before the dependency resolves.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   __shared__ int timed_out_s;
   __shared__ long long timeout_s;
   const int lane = threadIdx.x & 31;
@@ -112,14 +115,20 @@ ctx_exchange_merge_kernel(T* __restrict__ out, const float* __restrict__ exp_sum
     }
     __syncthreads();
     const size_t row_off = slot_off + ((size_t)rank * max_pairs + pair) * row_floats;
-    for (int d = threadIdx.x; d < head_size; d += blockDim.x) {
-      const float v = (part[d] + part[head_size + d] + part[2 * head_size + d] + part[3 * head_size + d]) * inv;
+    // 16-byte peer stores: row = {m, l, 0, 0 | o[0..D)}; thread t carries float4 number t of the row
+    for (int v4 = threadIdx.x; v4 < (head_size + kCtxRowPad) / 4; v4 += blockDim.x) {
+      float4 val;
+      if (v4 == 0) {
+        val = make_float4(mx, sum, 0.f, 0.f);
+      } else {
+        const int d = 4 * (v4 - 1);
+        val.x = (part[d] + part[head_size + d] + part[2 * head_size + d] + part[3 * head_size + d]) * inv;
+        val.y = (part[d + 1] + part[head_size + d + 1] + part[2 * head_size + d + 1] + part[3 * head_size + d + 1]) * inv;
+        val.z = (part[d + 2] + part[head_size + d + 2] + part[2 * head_size + d + 2] + part[3 * head_size + d + 2]) * inv;
+        val.w = (part[d + 3] + part[head_size + d + 3] + part[2 * head_size + d + 3] + part[3 * head_size + d + 3]) * inv;
+      }
       for (int r = 0; r < world; ++r)
-        reinterpret_cast<float*>(peers.buf[r] + hdr)[row_off + kCtxRowPad + d] = v;
-    }
-    if (threadIdx.x == 0) {
-      for (int r = 0; r < world; ++r)
-        *reinterpret_cast<float2*>(reinterpret_cast<float*>(peers.buf[r] + hdr) + row_off) = make_float2(mx, sum);
+        reinterpret_cast<float4*>(reinterpret_cast<float*>(peers.buf[r] + hdr) + row_off)[v4] = val;
     }
     __syncthreads();  // part[] is reused by the next pair
   }
@@ -203,7 +212,7 @@ int launch_ctx_exchange(void* out, const float* exp_sums, const float* max_logit
   const long long pairs = (long long)num_seqs * num_heads;
   B200_CHECK_ARG(pairs <= max_pairs, "ctx_shard: %lld (seq, head) pairs exceed the exchange buffer's %d",
                  pairs, max_pairs);
-  B200_CHECK_ARG(head_size % 2 == 0, "ctx_shard: odd head size");
+  B200_CHECK_ARG(head_size % 4 == 0, "ctx_shard: head size must be a multiple of 4");
   B200_CHECK_ARG(phases >= 1 && phases <= 3, "ctx_shard: phases must be 1 (publish), 2 (merge) or 3");
   CtxPeers peers{};
   for (int r = 0; r < world; ++r) {
@@ -217,11 +226,24 @@ int launch_ctx_exchange(void* out, const float* exp_sums, const float* max_logit
   const size_t wsmem = (size_t)4 * head_size * sizeof(float);
   (void)parts;
   const long long timeout = 4000000000LL;  // ~2 s of SM clocks: a missing peer must not hang the GPU
-#define B200_CTX_LAUNCH(T)                                                                       \
-  ctx_exchange_merge_kernel<T><<<blocks, 128, wsmem, stream>>>(                                  \
-      static_cast<T*>(out), exp_sums, max_logits, static_cast<const T*>(tmp_out), seq_lens,     \
-      num_heads, head_size, max_num_partitions, partition_tokens, wstride, (int)pairs, peers,   \
-      rank, world, max_pairs, epoch, phases, timeout)
+  // Programmatic dependent launch: the grid is scheduled while the partition pass (same stream) drains and
+  // parks in griddepcontrol.wait, which takes the launch latency off the step's critical path.
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(blocks);
+  cfg.blockDim = dim3(128);
+  cfg.dynamicSmemBytes = wsmem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const int pairs_i = (int)pairs;
+#define B200_CTX_LAUNCH(T)                                                                                   \
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, ctx_exchange_merge_kernel<T>, static_cast<T*>(out), exp_sums,         \
+                                  max_logits, static_cast<const T*>(tmp_out), seq_lens, num_heads, head_size, \
+                                  max_num_partitions, partition_tokens, wstride, pairs_i, peers, rank, world, \
+                                  max_pairs, epoch, phases, timeout))
   if (q_dtype == B200_DT_F16) B200_CTX_LAUNCH(__half);
   else if (q_dtype == B200_DT_BF16) B200_CTX_LAUNCH(__nv_bfloat16);
   else B200_CTX_LAUNCH(float);

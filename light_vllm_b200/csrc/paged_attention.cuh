@@ -37,7 +37,9 @@ struct AttnParams {
   const int32_t* seq_lens;      // [B]
   const float* alibi_slopes;    // [H] or null
   int num_heads, num_kv_heads, group;  // group = H / KH
-  int gchunks;                  // ceil(group / GROWS)
+  int gchunks;                  // ceil(group / rows_per_cta)
+  int rows_per_cta;             // q-heads of the group one CTA computes (<= GROWS; fewer = "head split"
+                                // for grids too small to fill the machine: more CTAs share each page via L2)
   int max_blocks_per_seq;
   int max_num_partitions;       // v2 only
   int partition_pages;          // v2: pages per 512-token partition; v1: 0

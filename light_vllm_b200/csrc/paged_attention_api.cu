@@ -109,14 +109,15 @@ paged_attention_v2_reduce_kernel(T* __restrict__ out, const float* __restrict__ 
 // b200_paged_attention_tuned / b200_paged_attention_plan only: the library keeps no mutable state
 // between calls and reads no environment variables (thread-per-GPU callers).
 struct Knobs {
-  int warps = 0, stages = 0, cluster = 0;
+  int warps = 0, stages = 0, cluster = 0, rows = 0;
 };
 
 struct Plan {
   AttnEntry entry;
   int grows, gchunks, nwarps, nstages, cluster, ctas_per_sm, num_sms;
+  int rows;                 // q-heads per CTA (<= grows; < group = head split)
   int v2_parts;             // v2: partitions per sequence at max_seq_len (1 = single pass)
-  int v2_partition_tokens;  // v2: context tokens per partition (multiple of 512)
+  int v2_partition_tokens;  // v2: context tokens per partition (>= 512, a multiple of the block size)
   size_t smem;
 };
 
@@ -128,7 +129,8 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
                  num_kv_heads);
   const int group = num_heads / num_kv_heads;
   pl.grows = (group > 8 && head_size <= 128) ? 16 : 8;
-  pl.gchunks = (group + pl.grows - 1) / pl.grows;
+  pl.rows = group < pl.grows ? group : pl.grows;
+  pl.gchunks = (group + pl.rows - 1) / pl.rows;
   AttnEntry e{nullptr, nullptr, nullptr};
   if (q_dtype == B200_DT_F16) {
     e = kv_dtype == B200_KV_AUTO       ? attn_lookup_f16_auto(head_size, block_size, pl.grows)
@@ -143,7 +145,8 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
   } else if (q_dtype == B200_DT_F32) {
     // fp32 queries run on the CUDA-core kernel (paged_attention_f32.cu): 1, 2 or 4 q-heads per CTA
     pl.grows = attn_f32_group_rows(group, head_size);
-    pl.gchunks = (group + pl.grows - 1) / pl.grows;
+    pl.rows = group < pl.grows ? group : pl.grows;
+    pl.gchunks = (group + pl.rows - 1) / pl.rows;
     e = attn_lookup_f32(head_size, block_size, kv_dtype, pl.grows);
   } else {
     set_error("Unsupported data type: query dtype %d", q_dtype);
@@ -179,7 +182,12 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
     if (pl.nwarps > 4) pl.nwarps = 4;
     while (pl.nwarps > 1 && (size_t)pl.nwarps * 2 * stage_bytes > (size_t)200 * 1024) pl.nwarps /= 2;
   }
-  const long long base = (long long)num_seqs * num_kv_heads * pl.gchunks;  // CTAs before any split
+  if (kn.rows > 0) {  // forced head split
+    pl.rows = kn.rows < pl.rows ? kn.rows : pl.rows;
+    pl.gchunks = (group + pl.rows - 1) / pl.rows;
+  }
+  long long base = (long long)num_seqs * num_kv_heads * pl.gchunks;  // CTAs before any split
+  if (base < 1) base = 1;
   int ns = kn.stages;
   if (ns <= 0) {
     // candidate A: ring that lets three CTAs share an SM (2..4 stages); candidate B: a deeper ring
@@ -210,13 +218,40 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
   pl.ctas_per_sm = e.occupancy(pl.nwarps, ns);
   if (pl.ctas_per_sm < 1) pl.ctas_per_sm = 1;
 
-  // v1 context split = cluster size.  Measured on B200 (profiles/r1_sweep_c2.md): an unsplit grid
-  // of >= one CTA per residency slot already reaches ~97 % of the HBM peak (partial waves do not
-  // matter for a bandwidth-bound kernel), while clusters cost co-scheduling and the DSMEM merge.
-  // So split only when the grid cannot fill the machine: the smallest power of two that gives at
-  // least half the residency slots (= every SM) a CTA, leaving every warp at least 2 pages
-  // (profiles/r1_sweep_grid.md: B=16 -> 2, B=32 -> 1, B<=4 -> 8 are the measured optima).
+  // ---- context split and head split ----
+  // v1 splits through a thread-block cluster (<= 8 CTAs, DSMEM merge), v2 through the caller's scratch.
+  // Measured on B200 (profiles/r1_sweep_c2.md): an unsplit grid of >= one CTA per residency slot already
+  // reaches ~97 % of the HBM peak, and clusters cost co-scheduling, so v1 splits only when the grid cannot
+  // fill the machine.  The op contract fixes the v2 scratch SHAPE ([B,H,ceil(max_seq_len/512)(,D)]) but its
+  // contents are scratch (never read by the caller, paged_attn.py:156-191): a partition may be any whole
+  // number of pages >= 512 tokens, so the partition count is chosen for the MACHINE -- one resident wave of
+  // ~1.5 CTAs per SM, pages dealt evenly -- not fixed at 512 tokens.  When even the
+  // finest split leaves most slots empty (B <= 4 at 8 kv heads), the q-heads of a GQA group are spread over
+  // several CTAs (head split): they read the same pages at the same time, so HBM still sees each page once
+  // and L2 serves the copies.
+  const long long slots = (long long)num_sms * pl.ctas_per_sm;
+  const int max_pages = (max_seq_len + block_size - 1) / block_size;
+  const int min_part_pages = kPartitionSize / block_size > 0 ? kPartitionSize / block_size : 1;
+  const int parts_max = max_pages > 0 ? (max_pages + min_part_pages - 1) / min_part_pages : 1;
   pl.cluster = 1;
+  pl.v2_parts = 1;
+  pl.v2_partition_tokens = kPartitionSize;
+  auto v1_split = [&](long long b) {
+    int s = 1;
+    while (s < 8 && 2 * b * s < slots && max_pages / (2 * s) >= 2 * pl.nwarps) s *= 2;
+    return s;
+  };
+  const long long finest = version == 1 ? (q_dtype == B200_DT_F32 ? 1 : 8) : parts_max;
+  // (measured, profiles/r2_sweep_small.md: the head split pays for v1 -- one launch, B = 1 x 8 Ki tokens 23.9 ->
+  // 18.6 us -- and changes nothing for v2, whose two launches set the floor at these sizes)
+  if (kn.rows <= 0 && q_dtype != B200_DT_F32 && version == 1) {
+    while (pl.rows > 1 && 2 * base * finest <= slots) {  // less than half the slots even at the finest split
+      pl.rows = (pl.rows + 1) / 2;
+      pl.gchunks = (group + pl.rows - 1) / pl.rows;
+      base = (long long)num_seqs * num_kv_heads * pl.gchunks;
+      if (base < 1) base = 1;
+    }
+  }
   if (version == 1) {
     const int forced = kn.cluster;
     if (q_dtype == B200_DT_F32) {
@@ -224,33 +259,29 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
     } else if (forced > 0) {
       pl.cluster = forced;
     } else {
-      const long long slots = (long long)num_sms * pl.ctas_per_sm;
-      const int max_pages = (max_seq_len + block_size - 1) / block_size;
-      int s = 1;
-      while (s < 8 && 2 * base * s < slots && max_pages / (2 * s) >= 2 * pl.nwarps) s *= 2;
-      pl.cluster = s;
+      pl.cluster = v1_split(base);
     }
-  }
-  // v2 context split through the caller's scratch.  The op contract fixes the scratch shape
-  // ([B,H,ceil(max_seq_len/512)(,D)]) but its contents are scratch (never read by the caller,
-  // paged_attn.py:156-191), so the partition length is a multiple m of 512 tokens chosen like the
-  // v1 split: as few, as long partitions as still give every residency slot about two CTAs.
-  // m = 1 reproduces the reference's geometry; when one partition covers max_seq_len the kernel
-  // writes `out` directly and the merge launch is skipped.
-  pl.v2_parts = 1;
-  pl.v2_partition_tokens = kPartitionSize;
-  if (version == 2) {
-    const int p512 = max_seq_len > 0 ? (max_seq_len + kPartitionSize - 1) / kPartitionSize : 1;
-    const long long slots = (long long)num_sms * pl.ctas_per_sm;
-    long long want = (2 * slots + base - 1) / base;  // partitions per sequence we would like
-    if (want < 1) want = 1;
-    if (want > p512) want = p512;
-    int m = (int)(p512 / want);
-    if (m < 1) m = 1;
-    const int forced = kn.cluster;  // tuning: "cluster" knob = forced m for v2
-    if (forced > 0) m = forced;
-    pl.v2_partition_tokens = kPartitionSize * m;
-    pl.v2_parts = (p512 + m - 1) / m;
+  } else {
+    int parts;
+    if (kn.cluster > 0) {  // tuning: "split" = forced partition count for v2
+      parts = kn.cluster < parts_max ? kn.cluster : parts_max;
+    } else {
+      // Measured (profiles/r2_sweep_small.md, tools/sweep_ctx_plan.sh): for grids that need a split at all
+      // the best partition count puts ~1.5 CTAs on every SM in ONE resident wave (4 x 16 Ki tokens: 7
+      // partitions 51.7 us, 27 partitions 56.5 us; 1 x 64 Ki: 32 partitions 53.1 us, 111 partitions 67.7 us);
+      // more, shorter partitions only add prologues, partial rows and reduce work, and counts that land
+      // just above a multiple of the residency (14-16 partitions x 32 CTAs on 444 slots) lose a wave.
+      long long want = (3LL * num_sms / 2 + base / 2) / base;
+      if (want < 1) want = 1;
+      if (want > parts_max) want = parts_max;
+      parts = (int)want;
+      (void)slots;
+    }
+    if (parts < 1) parts = 1;
+    int pp = max_pages > 0 ? (max_pages + parts - 1) / parts : min_part_pages;
+    if (pp < min_part_pages) pp = min_part_pages;
+    pl.v2_partition_tokens = pp * block_size;
+    pl.v2_parts = max_pages > 0 ? (max_pages + pp - 1) / pp : 1;
   }
   return B200_OK;
 }
@@ -311,6 +342,7 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
   p.num_kv_heads = num_kv_heads;
   p.group = num_heads / num_kv_heads;
   p.gchunks = pl.gchunks;
+  p.rows_per_cta = pl.rows;
   p.max_blocks_per_seq = max_num_blocks_per_seq;
   p.max_num_partitions = max_num_partitions;
   const bool split_v2 = (version == 2 && pl.v2_parts > 1) || ctx != nullptr;
@@ -438,6 +470,7 @@ static Knobs to_knobs(const b200_attn_tuning_t* t) {
     k.warps = t->num_warps;
     k.stages = t->num_stages;
     k.cluster = t->split;
+    k.rows = t->head_rows;
   }
   return k;
 }

@@ -57,8 +57,8 @@ paged_attention_f32_kernel(const __grid_constant__ AttnParams p) {
   const int seq = blockIdx.z;
   const int kvh = blockIdx.y / p.gchunks;
   const int gchunk = blockIdx.y - kvh * p.gchunks;
-  const int head0 = kvh * p.group + gchunk * GR;
-  const int gcount = min(GR, p.group - gchunk * GR);
+  const int head0 = kvh * p.group + gchunk * p.rows_per_cta;
+  const int gcount = min(p.rows_per_cta, p.group - gchunk * p.rows_per_cta);
   const int seq_len = p.seq_lens[seq];
   const int n_pages = (seq_len + BS - 1) / BS;
 

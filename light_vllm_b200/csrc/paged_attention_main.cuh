@@ -73,8 +73,8 @@ __global__ void __launch_bounds__(B200_ATTN_MAXT, B200_ATTN_MINB) paged_attentio
   const int seq = blockIdx.z;
   const int kvh = blockIdx.y / p.gchunks;
   const int gchunk = blockIdx.y - kvh * p.gchunks;
-  const int head0 = kvh * p.group + gchunk * GROWS;           // first q-head of this CTA
-  const int gcount = min(GROWS, p.group - gchunk * GROWS);    // real q-heads in this CTA
+  const int head0 = kvh * p.group + gchunk * p.rows_per_cta;           // first q-head of this CTA
+  const int gcount = min(p.rows_per_cta, p.group - gchunk * p.rows_per_cta);  // real q-heads in this CTA
   const int seq_len = p.seq_lens[seq];
   const int n_pages = (seq_len + BS - 1) / BS;
 

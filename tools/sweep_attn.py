@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Tuning / comparison harness (not part of the product): times paged_attention for a config under
-different launch plans (warps x ring stages x v1 cluster size) and, when oracle/_ref/libref_cuda.so
+different launch plans (warps x ring stages x split [x q-heads per CTA]; split = v1 cluster size or v2
+partitions per sequence) and, when oracle/_ref/libref_cuda.so
 is present, the reference's own CUDA kernel recompiled for sm_100a on the same inputs.
 
     python tools/sweep_attn.py --config c2 [--plans "4,3,4;4,3,1;8,2,2"] [--ref] [--reps 30]
@@ -95,10 +96,10 @@ def main():
 
     ab = algorithmic_bytes_attention(c)
     for plan in args.plans.split(";"):
-        w, s, cl = [int(x) for x in plan.split(",")]
+        tn = tuple(int(x) for x in plan.split(","))  # warps,stages,split[,head_rows]
         try:
-            us = time_it(ops, tuned_call((w, s, cl)))
-            info = _lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, 0, (w, s, cl))
+            us = time_it(ops, tuned_call(tn))
+            info = _lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, 0, tn)
             print(json.dumps({"impl": "b200", "config": args.config, "v": c["version"], "B": B,
                               "ctx": ctx, "plan": plan, "us": round(us, 2),
                               "GBps": round(ab / us / 1e3, 1), "resolved": info}), flush=True)
