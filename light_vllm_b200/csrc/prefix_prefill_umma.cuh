@@ -3,28 +3,25 @@
 // (light_vllm/decoding/backends/attention/ops/prefix_prefill.py:674-811) for head size 128,
 // fp16 / bf16, no ALiBi, no sliding window.  Everything else stays on prefix_prefill.cu.
 //
-// One CTA (20 warps, one per SM) owns (sequence, KV head, tile of 256 / G query tokens): its 256 rows
+// One CTA (16 warps, one per SM) owns (sequence, KV head, tile of 256 / G query tokens): its 256 rows
 // (query token, q-head of the GQA group) are two 128-row M tiles that share every K/V tile.  Keys are
 // consumed in steps of 64.
 //
-//   warps 0-7 / 8-15  softmax of M tile 0 / 1: TWO threads per row (= TMEM lane), one per 32-column half of
-//                     the step -- one thread per row left each scheduler with a single softmax warp per M
-//                     tile and the exponentials latency-bound (profiles/r2_prefix.md).  S comes back with
-//                     tcgen05.ld, the half-row maxima meet through shared memory and a 64-thread named
-//                     barrier, P = exp2(S*c - m) is written
+//   warps 0-3 / 4-7   softmax warpgroup of M tile 0 / 1: one thread per row (= TMEM lane).  S comes back
+//                     with tcgen05.ld, the row maximum needs no shuffle, P = exp2(S*c - m) is written
 //                     back over S as 16-bit pairs (tcgen05.st) and becomes the A operand of P.V straight
 //                     from TMEM.  The output accumulator is only rescaled when a row's maximum grew by
 //                     more than 2^8 (the stale maximum stays the reference point otherwise), so the
 //                     TMEM round trip of O is rare.
-//   warps 16-17       gather: the cache keeps a K page as [D/8][BS][8] and a V page as [D][BS]; neither is
+//   warps 8-11        gather: the cache keeps a K page as [D/8][BS][8] and a V page as [D][BS]; neither is
 //                     an operand layout tcgen05.mma can address across pages.  Both ARE permutations of
-//                     16-byte chunks of the K-major SWIZZLE_128B operand tiles, so 64 threads move a
-//                     64-key K tile and V tile with 32 cp.async (LDGSTS, 16 B) each -- one block-table
+//                     16-byte chunks of the K-major SWIZZLE_128B operand tiles, so 128 threads move a
+//                     64-key K tile and V tile with 16 cp.async (LDGSTS, 16 B) each -- one block-table
 //                     lookup per thread and tile, global reads in 128..512-byte runs, bank-conflict-free
 //                     shared-memory writes, no register staging, no extra pass over HBM; completion is
 //                     signalled by cp.async.mbarrier.arrive, so the gather never blocks on its own
 //                     copies.  New tokens arrive as pages too (prefix_stage_kv_kernel): one gather path.
-//   warps 18 / 19     one elected thread per M tile issues its tcgen05.mma stream: S_w = Q_w K^T (SS form,
+//   warps 12 / 13     one elected thread per M tile issues its tcgen05.mma stream: S_w = Q_w K^T (SS form,
 //                     128x64x16) and O_w += P_w V (TS form, 128x128x16), and signals mbarriers with
 //                     tcgen05.commit.  Issue sits under elect.sync so that ptxas keeps descriptors in
 //                     uniform registers (a lane == 0 branch costs a uniform-loop per instruction).
@@ -47,16 +44,14 @@
 
 namespace b200 {
 
-constexpr int kUmmaThreads = 640;
+constexpr int kUmmaThreads = 512;
 constexpr int kUmmaRows = 256;          // rows per CTA (two M tiles)
 constexpr int kUmmaKeys = 64;           // keys per step
 constexpr uint32_t kUmmaQTile = 32768;  // bytes of one 128-row x 128-d Q tile
 constexpr uint32_t kUmmaKVTile = 16384; // bytes of one 64-key K (or V) tile
 constexpr int kUmmaKStages = 5, kUmmaVStages = 4;
 constexpr uint32_t kUmmaBarBytes = 8 * (2 * kUmmaKStages + 2 * kUmmaVStages + 4 + 4 + 2) + 16;
-constexpr uint32_t kUmmaXchBytes = 3 * 2048;  // half-row maxima (two step parities) and row sums, [w][h][128] floats
-constexpr uint32_t kUmmaSmem =
-    2 * kUmmaQTile + (kUmmaKStages + kUmmaVStages) * kUmmaKVTile + kUmmaBarBytes + kUmmaXchBytes + 1024;
+constexpr uint32_t kUmmaSmem = 2 * kUmmaQTile + (kUmmaKStages + kUmmaVStages) * kUmmaKVTile + kUmmaBarBytes + 1024;
 
 template <typename T, int BS>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
@@ -100,21 +95,20 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
                  bars = v_ring + kUmmaVStages * kUmmaKVTile;
   const uint32_t k_full = bars, k_empty = k_full + 8 * kUmmaKStages, v_full = k_empty + 8 * kUmmaKStages,
                  v_empty = v_full + 8 * kUmmaVStages, s_full = v_empty + 8 * kUmmaVStages,  // [w][buffer]
-                 p_full = s_full + 32, o_ready = p_full + 32, slot = o_ready + 16,  // p_full: [w][buffer]
-                 xch = bars + kUmmaBarBytes;
+                 p_full = s_full + 32, o_ready = p_full + 32, slot = o_ready + 16;  // p_full: [w][buffer]
 
   if (tid == 0) {
     for (int i = 0; i < kUmmaKStages; ++i) {
-      mbar_init(k_full + 8 * i, 64);
+      mbar_init(k_full + 8 * i, 128);
       mbar_init(k_empty + 8 * i, nq);
     }
     for (int i = 0; i < kUmmaVStages; ++i) {
-      mbar_init(v_full + 8 * i, 64);
+      mbar_init(v_full + 8 * i, 128);
       mbar_init(v_empty + 8 * i, nq);
     }
     for (int i = 0; i < 4; ++i) {
       mbar_init(s_full + 8 * i, 1);
-      mbar_init(p_full + 8 * i, 256);
+      mbar_init(p_full + 8 * i, 128);
     }
     for (int i = 0; i < 2; ++i) mbar_init(o_ready + 8 * i, 1);
     mbar_fence_init();
@@ -124,7 +118,9 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   // ---- Q: rows (token, head) -> two K-major SWIZZLE_128B tiles (padding rows repeat the last token) ----
   {
     const T* qg = static_cast<const T*>(p.q);
-    for (int id = tid; id < kUmmaRows * 16; id += kUmmaThreads) {
+#pragma unroll
+    for (int i = 0; i < kUmmaRows * 16 / kUmmaThreads; ++i) {
+      const int id = tid + kUmmaThreads * i;
       const int R = id >> 4, c = id & 15;
       if (R < 128 * nq) {
         const int ti = min(R / G, tile_tokens - 1);
@@ -145,64 +141,58 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   uint32_t tmem;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(slot));
 
-  // 20 warps x 96 registers fill the register file exactly: no setmaxnreg (it only moves registers inside
-  // the CTA's own pool, and ptxas kept the 24-warp variant at 80 registers whatever the increase asked for).
-  if (warp < 16) {
-    // ============ softmax: two warpgroups per M tile, two threads per row (one per half of the step) ============
-    // warp = 8 w + 4 h + q: M tile w, column half h of the 64-key step, TMEM lane quadrant q (a warp may
-    // only touch the lanes of quadrant warp % 4).  The two threads of a row exchange their half-row maxima
-    // through shared memory and a 64-thread named barrier, so both take the same (lazy) rescale decision.
-    const int w = warp >> 3;
+  if (warp < 8) {
+    setmaxnreg_inc<192>();
+  } else {
+    setmaxnreg_dec<64>();
+  }
+
+  if (warp < 8) {
+    // ======================= softmax warpgroups: one thread per row =======================
+    const int w = warp >> 2;
     if (w < nq) {
-      const int q4 = warp & 3, h = (warp >> 2) & 1;
-      const int r = q4 * 32 + lane;
+      const int r = (warp & 3) * 32 + lane;
       const int R = w * 128 + r;
       const int ti = R / G;
       const bool valid = ti < tile_tokens;
       const int iq = m0 + min(ti, tile_tokens - 1);  // query index among the new tokens
-      const uint32_t lane_bits = (uint32_t)(q4 * 32) << 16;
+      const uint32_t lane_bits = (uint32_t)((warp & 3) * 32) << 16;
       const uint32_t t_s = tmem + lane_bits + (uint32_t)w * 128u;
-      const uint32_t t_o = tmem + lane_bits + 256u + (uint32_t)w * 128u + 64u * (uint32_t)h;  // my half of O
-      const int pair_bar = 1 + w * 4 + q4;  // named barrier of the two warps that share these 32 rows
-      const uint32_t xme = xch + 4u * (uint32_t)((w * 2 + h) * 128 + r), xot = xch + 4u * (uint32_t)((w * 2 + (h ^ 1)) * 128 + r);
+      const uint32_t t_o = tmem + lane_bits + 256u + (uint32_t)w * 128u;
       const float c2 = p.scale_log2;
       float m_ref = kNInf, l = 0.f;
       for (int j = 0; j < nt; ++j) {
         const int b = j & 1;
         mbar_wait_wd(s_full + 8 * (2 * w + b), (uint32_t)((j >> 1) & 1));
         fence_after_sync();
-        uint32_t s[32];
-        tmem_ld32(t_s + 64 * b + 32 * h, s);
+        uint32_t s[2][32];
+        tmem_ld32(t_s + 64 * b, s[0]);
+        tmem_ld32(t_s + 64 * b + 32, s[1]);
         tmem_wait_ld();
-        // visible keys of this row in the step: a prefix [0, lim) of its 64 columns; mine are [32 h, 32 h + 32)
+        // visible keys of this row in the tile: a prefix [0, lim)
         int lim;
         if (j < n_ctx_tiles)
           lim = min(KT, ctx - KT * j);
         else
           lim = min(KT, max(0, iq - KT * (j - n_ctx_tiles) + 1));
-        lim -= 32 * h;
-        if (__any_sync(FULL, lim < 32)) {
+        if (__any_sync(FULL, lim < KT)) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (i >= lim) s[i] = __float_as_uint(kNInf);
+          for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (32 * c + i >= lim) s[c][i] = __float_as_uint(kNInf);
         }
         float mx0 = kNInf, mx1 = kNInf, mx2 = kNInf, mx3 = kNInf;
 #pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          mx0 = fmaxf(mx0, __uint_as_float(s[i]));
-          mx1 = fmaxf(mx1, __uint_as_float(s[i + 1]));
-          mx2 = fmaxf(mx2, __uint_as_float(s[i + 2]));
-          mx3 = fmaxf(mx3, __uint_as_float(s[i + 3]));
-        }
-        const float mhalf = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-        // exchange with the thread that holds the other half of this row (slots alternate with the step
-        // parity: a slot is rewritten two steps later, behind the next barrier)
-        const uint32_t par_off = (uint32_t)b * 2048u;
-        asm volatile("st.shared.f32 [%0], %1;" ::"r"(xme + par_off), "f"(mhalf) : "memory");
-        named_bar_sync(pair_bar, 64);
-        float mother;
-        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(mother) : "r"(xot + par_off) : "memory");
-        const float mloc = fmaxf(mhalf, mother) * c2;
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            mx0 = fmaxf(mx0, __uint_as_float(s[c][i]));
+            mx1 = fmaxf(mx1, __uint_as_float(s[c][i + 1]));
+            mx2 = fmaxf(mx2, __uint_as_float(s[c][i + 2]));
+            mx3 = fmaxf(mx3, __uint_as_float(s[c][i + 3]));
+          }
+        const float mloc = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * c2;
         // lazy rescale: keep the stale reference maximum unless the row maximum outgrew it by 2^8
         float alpha = 1.f;
         bool resc = false;
@@ -215,51 +205,46 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
           resc = true;
         }
         if (j > 0 && __any_sync(FULL, resc)) {
-          // O_w must hold every product up to step j - 1 before it is scaled; each thread scales its half
+          // O_w must hold every product up to step j - 1 before it is scaled
           mbar_wait_wd(o_ready + 8 * w, (uint32_t)((j - 1) & 1));
           fence_after_sync();
-          // (8 columns at a time: this rare path must not raise the register peak of the loop around it)
-#pragma unroll 1
-          for (int c = 0; c < 8; ++c) {
-            uint32_t o[8];
-            tmem_ld8(t_o + 8 * c, o);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t o[32];
+            tmem_ld32(t_o + 32 * c, o);
             tmem_wait_ld();
 #pragma unroll
-            for (int i = 0; i < 8; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            tmem_st8(t_o + 8 * c, o);
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st32(t_o + 32 * c, o);
           }
         }
         const float neg_m = m_ref == kNInf ? 0.f : -m_ref;
         float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
-        uint32_t pk[16];
+        uint32_t pk[32];
 #pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          const float e0 = fast_exp2(fmaf(__uint_as_float(s[i]), c2, neg_m));
-          const float e1 = fast_exp2(fmaf(__uint_as_float(s[i + 1]), c2, neg_m));
-          const float e2 = fast_exp2(fmaf(__uint_as_float(s[i + 2]), c2, neg_m));
-          const float e3 = fast_exp2(fmaf(__uint_as_float(s[i + 3]), c2, neg_m));
-          l0 += e0;
-          l1 += e1;
-          l2 += e2;
-          l3 += e3;
-          pk[i / 2] = MmaOp<T>::pack(e0, e1);
-          pk[i / 2 + 1] = MmaOp<T>::pack(e2, e3);
+        for (int c = 0; c < 2; ++c) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            const float e0 = fast_exp2(fmaf(__uint_as_float(s[c][i]), c2, neg_m));
+            const float e1 = fast_exp2(fmaf(__uint_as_float(s[c][i + 1]), c2, neg_m));
+            const float e2 = fast_exp2(fmaf(__uint_as_float(s[c][i + 2]), c2, neg_m));
+            const float e3 = fast_exp2(fmaf(__uint_as_float(s[c][i + 3]), c2, neg_m));
+            l0 += e0;
+            l1 += e1;
+            l2 += e2;
+            l3 += e3;
+            pk[16 * c + i / 2] = MmaOp<T>::pack(e0, e1);
+            pk[16 * c + i / 2 + 1] = MmaOp<T>::pack(e2, e3);
+          }
         }
-        // P over the first 32 columns of this S buffer: my 16 of them.  The other thread's S columns that I
-        // overwrite are in its registers already (it passed the barrier after its tcgen05.ld completed).
-        tmem_st16(t_s + 64 * b + 16 * h, pk);
+        tmem_st32(t_s + 64 * b, pk);  // P over the first 32 columns of this S buffer (S is in registers)
         l += (l0 + l1) + (l2 + l3);
         tmem_wait_st();
         fence_before_sync();
         // per S buffer: the softmax may finish step j + 1 before the MMA thread has looked at step j
         mbar_arrive(p_full + 8 * (2 * w + b));
       }
-      // ---- epilogue: O / l -> out (row sum = both halves; each thread writes 64 of the 128 columns) ----
-      asm volatile("st.shared.f32 [%0], %1;" ::"r"(xme + 4096u), "f"(l) : "memory");
-      named_bar_sync(pair_bar, 64);
-      float lother;
-      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(lother) : "r"(xot + 4096u) : "memory");
-      l += lother;
+      // ---- epilogue: O / l -> out ----
       // o_ready has completed nt - 2 phases for certain (S(nt-1) was issued behind P.V(nt-3)); walk the
       // last two one by one -- a parity wait can only tell "this phase" from "the next"
       if (nt >= 2) mbar_wait_wd(o_ready + 8 * w, (uint32_t)((nt - 2) & 1));
@@ -267,9 +252,9 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
       fence_after_sync();
       const float inv = l > 0.f ? 1.f / l : 0.f;
       T* orow = static_cast<T*>(p.out) + (start + m0 + min(ti, tile_tokens - 1)) * p.o_s0 +
-                (int64_t)(kvh * G + R % G) * p.o_s1 + 64 * h;
+                (int64_t)(kvh * G + R % G) * p.o_s1;
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      for (int c = 0; c < 4; ++c) {
         uint32_t o[32];
         tmem_ld32(t_o + 32 * c, o);
         tmem_wait_ld();
@@ -286,21 +271,21 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
         }
       }
     }
-  } else if (warp < 18) {
+  } else if (warp < 12) {
     // ======================= gather warps: pages -> swizzled operand tiles =======================
-    // 8 groups of 8 threads: group kg serves the 8 keys [8 kg, +8) of the tile; for K a thread moves the 16
-    // d chunks of its key (lane = key), for V the rows d = 8 i + lane of its 8-key chunk.  Every thread
-    // therefore touches one page per tile.
-    const int pt = tid - 512;
-    const int kg = pt >> 3, l8 = pt & 7;
+    // 16 groups of 8 threads: group g serves the 8 keys [8 (g & 7), +8) of the tile; for K it moves the
+    // d chunks [8 (g >> 3), +8) of its key (lane = key), for V the rows d = 64 (g >> 3) + 8 i + lane of
+    // its 8-key chunk.  Every thread therefore touches one page per tile.
+    const int pt = tid - 256;
+    const int g = pt >> 3, l8 = pt & 7, kg = g & 7, hi = g >> 3;
     const unsigned char* kbase = static_cast<const unsigned char*>(p.k_cache) + (int64_t)kvh * p.kc_hs * 2;
     const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (int64_t)kvh * p.vc_hs * 2;
     const int32_t* bt = p.block_tables + (int64_t)seq * p.max_blocks_per_seq;
     const unsigned char* sbase =
         p.kv_scratch + (((int64_t)(start / BS) + seq) * p.num_kv_heads + kvh) * SLICE_BYTES;
     const int64_t slice_stride = (int64_t)p.num_kv_heads * SLICE_BYTES;
-    const uint32_t k_off = (uint32_t)(8 * kg + l8) * 128u;
-    const uint32_t v_off = (uint32_t)l8 * 128u + (uint32_t)((kg ^ l8) << 4);
+    const uint32_t k_off = (uint32_t)hi * 8192u + (uint32_t)(8 * kg + l8) * 128u;
+    const uint32_t v_off = (uint32_t)(64 * hi + l8) * 128u + (uint32_t)((kg ^ l8) << 4);
     int ks = 0, kround = 0, vs = 0, vround = 0;  // ring positions of tile j, times each ring wrapped
     for (int j = 0; j < nt; ++j) {
       const bool is_ctx = j < n_ctx_tiles;
@@ -320,12 +305,11 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
       }
       {
         if (kround > 0) mbar_wait_wd(k_empty + 8 * ks, (uint32_t)((kround - 1) & 1));
-        const unsigned char* src = kpage + (toff + l8) * 16;
+        const unsigned char* src = kpage + (toff + l8) * 16 + hi * 8 * BS * 16;
         const uint32_t nb = l8 < nval ? 16u : 0u;
         const uint32_t dst = k_ring + (uint32_t)ks * kUmmaKVTile + k_off;
 #pragma unroll
-        for (int c = 0; c < 16; ++c)
-          cp_async16(dst + (uint32_t)(c >> 3) * 8192u + (uint32_t)(((c & 7) ^ l8) << 4), src + c * BS * 16, nb);
+        for (int i = 0; i < 8; ++i) cp_async16(dst + (uint32_t)((i ^ l8) << 4), src + i * BS * 16, nb);
         cp_async_arrive_noinc(k_full + 8 * ks);
         if (++ks == kUmmaKStages) {
           ks = 0;
@@ -334,11 +318,11 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
       }
       {
         if (vround > 0) mbar_wait_wd(v_empty + 8 * vs, (uint32_t)((vround - 1) & 1));
-        const unsigned char* src = vpage + toff * 2 + l8 * BS * 2;
+        const unsigned char* src = vpage + toff * 2 + (64 * hi + l8) * BS * 2;
         const uint32_t nb = nval > 0 ? 16u : 0u;
         const uint32_t dst = v_ring + (uint32_t)vs * kUmmaKVTile + v_off;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) cp_async16(dst + (uint32_t)i * 1024u, src + i * 8 * BS * 2, nb);
+        for (int i = 0; i < 8; ++i) cp_async16(dst + (uint32_t)i * 1024u, src + i * 8 * BS * 2, nb);
         if (is_ctx && nval > 0 && nval < 8) {
           // last context page: slots past ctx_len may hold anything (NaN included); P is 0 there, but
           // 0 * NaN is not -- clear them in the V tile (staged new-token pages are already zero filled)
@@ -349,7 +333,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
           for (int wd = 0; wd < 4; ++wd)
             mk[wd] = (2 * wd < nval ? 0x0000ffffu : 0u) | (2 * wd + 1 < nval ? 0xffff0000u : 0u);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
+          for (int i = 0; i < 8; ++i) {
             const uint32_t a = dst + (uint32_t)i * 1024u;
             uint32_t x, y, z, u;
             asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(u) : "r"(a));
@@ -373,12 +357,12 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
     }
     cp_async_commit();
     cp_async_wait_all();  // nothing of this thread is still in flight when the CTA winds down
-  } else if (warp < 18 + nq) {
-    // ======================= MMA issuers: warp 18 for M tile 0, warp 19 for M tile 1 =======================
+  } else if (warp < 12 + nq) {
+    // ======================= MMA issuers: warp 12 for M tile 0, warp 13 for M tile 1 =======================
     // Two independent instruction streams (disjoint TMEM, shared read-only K/V tiles): while one thread
     // polls its barriers the other one's MMAs keep the tensor pipe fed.  A K/V ring slot is free once
     // BOTH have committed past it (empty barriers count nq arrivals).
-    const int w = warp - 18;
+    const int w = warp - 12;
     constexpr uint32_t idesc_s = idesc_f16(FMT, 128, KT);
     constexpr uint32_t idesc_o = idesc_f16(FMT, 128, 128);
     const uint32_t t_sw = tmem + (uint32_t)w * 128u, t_ow = tmem + 256u + (uint32_t)w * 128u;
