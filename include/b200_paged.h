@@ -256,7 +256,7 @@ int b200_context_attention_fwd(
 /* Same call with the tile loop chosen by the caller (tests, benchmarks, autotuning; per call, no
  * global state).  AUTO = b200_context_attention_fwd.  MMA_SYNC: csrc/prefix_prefill.cu (every head size,
  * ALiBi, sliding window, fp32 on CUDA cores).  TCGEN05: csrc/prefix_prefill_umma.cuh (tcgen05.mma with
- * TMEM accumulators, 256-row tiles; head size 128, fp16 / bf16, no ALiBi / window, needs kv_scratch and
+ * TMEM accumulators, 256-row tiles; head size 64 or 128, fp16 / bf16, no ALiBi / window, needs kv_scratch and
  * 16-byte aligned q / out rows -- B200_ERR_UNSUPPORTED otherwise). */
 #define B200_PREFIX_PATH_AUTO 0
 #define B200_PREFIX_PATH_MMA_SYNC 1

@@ -17,7 +17,7 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
                           sliding_window: Optional[int] = None, use_scratch: bool = True,
                           path: str = "auto") -> None:
     """``path``: ``"auto"`` (default) lets the library pick the tile loop -- the tcgen05 / TMEM kernel
-    (``csrc/prefix_prefill_umma.cuh``) for head size 128 fp16 / bf16 without ALiBi / window once a
+    (``csrc/prefix_prefill_umma.cuh``) for head size 64 / 128 fp16 / bf16 without ALiBi / window once a
     sequence brings >= 128 (token, head) rows, the ``mma.sync`` kernel otherwise; ``"tcgen05"`` /
     ``"mma_sync"`` force one (tests, benchmarks; unsupported combinations raise).
 

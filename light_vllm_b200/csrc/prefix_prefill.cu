@@ -613,27 +613,27 @@ int launch_prefix_stage(const PrefixParams& p, int num_seqs, int max_query_len, 
   return B200_OK;
 }
 
-// Can the tcgen05 tile loop (prefix_prefill_umma.cuh) serve this call?  Head 128, no ALiBi / window,
+// Can the tcgen05 tile loop (prefix_prefill_umma.cuh) serve this call?  Head 64 or 128, no ALiBi / window,
 // staged new tokens, 16-byte aligned q / out rows, a GQA group that fits one 128-row M tile.
 template <int D>
 bool umma_eligible(const PrefixParams& p) {
   auto a16 = [](const void* ptr) { return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0; };
-  return D == 128 && p.alibi_slopes == nullptr && p.sliding_window == 0 && p.kv_scratch != nullptr &&
+  return (D == 128 || D == 64) && p.alibi_slopes == nullptr && p.sliding_window == 0 && p.kv_scratch != nullptr &&
          p.group <= 128 && a16(p.q) && a16(p.out) && p.q_s0 % 8 == 0 && p.q_s1 % 8 == 0 && p.o_s0 % 8 == 0 &&
          p.o_s1 % 8 == 0;
 }
 
-template <typename T, int BS>
+template <typename T, int D, int BS>
 int launch_prefix_umma(PrefixParams& p, int num_seqs, int max_query_len, int device, cudaStream_t stream) {
   p.tok_tile = kUmmaRows / p.group;
-  auto kern = context_attention_umma_kernel<T, BS>;
+  auto kern = context_attention_umma_kernel<T, D, BS>;
   static std::atomic<int> configured[64];
   const int slot = device & 63;
   if (!configured[slot].load(std::memory_order_acquire)) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUmmaSmem));
     configured[slot].store(1, std::memory_order_release);
   }
-  const int rc = launch_prefix_stage<T, 128, BS>(p, num_seqs, max_query_len, stream);
+  const int rc = launch_prefix_stage<T, D, BS>(p, num_seqs, max_query_len, stream);
   if (rc != B200_OK) return rc;
   const int tiles = (max_query_len + p.tok_tile - 1) / p.tok_tile;
   B200_CHECK_ARG(p.num_kv_heads <= 65535 && num_seqs <= 65535, "context_attention_fwd: grid too large");
@@ -646,19 +646,19 @@ int launch_prefix_umma(PrefixParams& p, int num_seqs, int max_query_len, int dev
 
 template <typename T, int D, int BS>
 int launch_prefix(PrefixParams& p, int num_seqs, int max_query_len, int device, cudaStream_t stream, int path) {
-  if constexpr (D == 128) {
+  if constexpr (D == 128 || D == 64) {
     const bool can = umma_eligible<D>(p);
     if (path == B200_PREFIX_PATH_TCGEN05 && !can) {
-      set_error("context_attention_fwd: the tcgen05 path needs head size 128, no ALiBi / sliding window, "
+      set_error("context_attention_fwd: the tcgen05 path needs head size 64 or 128, no ALiBi / sliding window, "
                 "a staging scratch and 16-byte aligned q / out rows");
       return B200_ERR_UNSUPPORTED;
     }
     // auto: the 256-row tile pays once a sequence brings at least one full M tile of rows
     if (can && (path == B200_PREFIX_PATH_TCGEN05 ||
                 (path == B200_PREFIX_PATH_AUTO && (int64_t)max_query_len * p.group >= 128)))
-      return launch_prefix_umma<T, BS>(p, num_seqs, max_query_len, device, stream);
+      return launch_prefix_umma<T, D, BS>(p, num_seqs, max_query_len, device, stream);
   } else if (path == B200_PREFIX_PATH_TCGEN05) {
-    set_error("context_attention_fwd: the tcgen05 path needs head size 128 (got %d)", D);
+    set_error("context_attention_fwd: the tcgen05 path needs head size 64 or 128 (got %d)", D);
     return B200_ERR_UNSUPPORTED;
   }
   constexpr int GROWS = D <= 128 ? 16 : 8;

@@ -1,6 +1,6 @@
 // Prefix / chunked-prefill attention on the 5th-generation tensor cores (tcgen05.mma, accumulators in
 // TMEM): the compute-bound tile loop of context_attention_fwd
-// (light_vllm/decoding/backends/attention/ops/prefix_prefill.py:674-811) for head size 128,
+// (light_vllm/decoding/backends/attention/ops/prefix_prefill.py:674-811) for head size 64 or 128,
 // fp16 / bf16, no ALiBi, no sliding window.  Everything else stays on prefix_prefill.cu.
 //
 // One CTA (16 warps, one per SM) owns (sequence, KV head, tile of 256 / G query tokens): its 256 rows
@@ -53,12 +53,13 @@ constexpr int kUmmaKStages = 5, kUmmaVStages = 4;
 constexpr uint32_t kUmmaBarBytes = 8 * (2 * kUmmaKStages + 2 * kUmmaVStages + 4 + 4 + 2) + 16;
 constexpr uint32_t kUmmaSmem = 2 * kUmmaQTile + (kUmmaKStages + kUmmaVStages) * kUmmaKVTile + kUmmaBarBytes + 1024;
 
-template <typename T, int BS>
+template <typename T, int D, int BS>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
 context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   using namespace umma;
-  constexpr int D = 128;
+  static_assert(D == 64 || D == 128, "head size 64 or 128");
   constexpr int KT = kUmmaKeys;
+  constexpr int KCH = D / 8;  // 16-byte chunks per key (K) / per 8-key chunk column (Q rows)
   constexpr int PAGE_BYTES = D * BS * 2;
   constexpr int SLICE_BYTES = 2 * PAGE_BYTES;
   constexpr int FMT = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
@@ -119,9 +120,9 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
   {
     const T* qg = static_cast<const T*>(p.q);
 #pragma unroll
-    for (int i = 0; i < kUmmaRows * 16 / kUmmaThreads; ++i) {
+    for (int i = 0; i < kUmmaRows * KCH / kUmmaThreads; ++i) {
       const int id = tid + kUmmaThreads * i;
-      const int R = id >> 4, c = id & 15;
+      const int R = id / KCH, c = id % KCH;
       if (R < 128 * nq) {
         const int ti = min(R / G, tile_tokens - 1);
         const int head = kvh * G + R % G;
@@ -209,7 +210,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
           mbar_wait_wd(o_ready + 8 * w, (uint32_t)((j - 1) & 1));
           fence_after_sync();
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
+          for (int c = 0; c < D / 32; ++c) {
             uint32_t o[32];
             tmem_ld32(t_o + 32 * c, o);
             tmem_wait_ld();
@@ -254,7 +255,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
       T* orow = static_cast<T*>(p.out) + (start + m0 + min(ti, tile_tokens - 1)) * p.o_s0 +
                 (int64_t)(kvh * G + R % G) * p.o_s1;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < D / 32; ++c) {
         uint32_t o[32];
         tmem_ld32(t_o + 32 * c, o);
         tmem_wait_ld();
@@ -273,8 +274,8 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
     }
   } else if (warp < 12) {
     // ======================= gather warps: pages -> swizzled operand tiles =======================
-    // 16 groups of 8 threads: group g serves the 8 keys [8 (g & 7), +8) of the tile; for K it moves the
-    // d chunks [8 (g >> 3), +8) of its key (lane = key), for V the rows d = 64 (g >> 3) + 8 i + lane of
+    // 16 groups of 8 threads: group g serves the 8 keys [8 (g & 7), +8) of the tile; for K it moves half of
+    // the d chunks of its key (lane = key; half g >> 3), for V the rows d = (D/2) (g >> 3) + 8 i + lane of
     // its 8-key chunk.  Every thread therefore touches one page per tile.
     const int pt = tid - 256;
     const int g = pt >> 3, l8 = pt & 7, kg = g & 7, hi = g >> 3;
@@ -284,8 +285,8 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
     const unsigned char* sbase =
         p.kv_scratch + (((int64_t)(start / BS) + seq) * p.num_kv_heads + kvh) * SLICE_BYTES;
     const int64_t slice_stride = (int64_t)p.num_kv_heads * SLICE_BYTES;
-    const uint32_t k_off = (uint32_t)hi * 8192u + (uint32_t)(8 * kg + l8) * 128u;
-    const uint32_t v_off = (uint32_t)(64 * hi + l8) * 128u + (uint32_t)((kg ^ l8) << 4);
+    const uint32_t k_off = (uint32_t)(8 * kg + l8) * 128u;
+    const uint32_t v_off = (uint32_t)((D / 2) * hi + l8) * 128u + (uint32_t)((kg ^ l8) << 4);
     int ks = 0, kround = 0, vs = 0, vround = 0;  // ring positions of tile j, times each ring wrapped
     for (int j = 0; j < nt; ++j) {
       const bool is_ctx = j < n_ctx_tiles;
@@ -305,11 +306,14 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
       }
       {
         if (kround > 0) mbar_wait_wd(k_empty + 8 * ks, (uint32_t)((kround - 1) & 1));
-        const unsigned char* src = kpage + (toff + l8) * 16 + hi * 8 * BS * 16;
+        const unsigned char* src = kpage + (toff + l8) * 16;
         const uint32_t nb = l8 < nval ? 16u : 0u;
         const uint32_t dst = k_ring + (uint32_t)ks * kUmmaKVTile + k_off;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) cp_async16(dst + (uint32_t)((i ^ l8) << 4), src + i * BS * 16, nb);
+        for (int i = 0; i < KCH / 2; ++i) {
+          const int c = (KCH / 2) * hi + i;  // d chunk: slab c / 8, swizzled position (c % 8) ^ (row % 8)
+          cp_async16(dst + (uint32_t)(c >> 3) * 8192u + (uint32_t)(((c & 7) ^ l8) << 4), src + c * BS * 16, nb);
+        }
         cp_async_arrive_noinc(k_full + 8 * ks);
         if (++ks == kUmmaKStages) {
           ks = 0;
@@ -318,11 +322,11 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
       }
       {
         if (vround > 0) mbar_wait_wd(v_empty + 8 * vs, (uint32_t)((vround - 1) & 1));
-        const unsigned char* src = vpage + toff * 2 + (64 * hi + l8) * BS * 2;
+        const unsigned char* src = vpage + toff * 2 + ((D / 2) * hi + l8) * BS * 2;
         const uint32_t nb = nval > 0 ? 16u : 0u;
         const uint32_t dst = v_ring + (uint32_t)vs * kUmmaKVTile + v_off;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) cp_async16(dst + (uint32_t)i * 1024u, src + i * 8 * BS * 2, nb);
+        for (int i = 0; i < D / 16; ++i) cp_async16(dst + (uint32_t)i * 1024u, src + i * 8 * BS * 2, nb);
         if (is_ctx && nval > 0 && nval < 8) {
           // last context page: slots past ctx_len may hold anything (NaN included); P is 0 there, but
           // 0 * NaN is not -- clear them in the V tile (staged new-token pages are already zero filled)
@@ -333,7 +337,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
           for (int wd = 0; wd < 4; ++wd)
             mk[wd] = (2 * wd < nval ? 0x0000ffffu : 0u) | (2 * wd + 1 < nval ? 0xffff0000u : 0u);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
+          for (int i = 0; i < D / 16; ++i) {
             const uint32_t a = dst + (uint32_t)i * 1024u;
             uint32_t x, y, z, u;
             asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(u) : "r"(a));
@@ -364,14 +368,14 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
     // BOTH have committed past it (empty barriers count nq arrivals).
     const int w = warp - 12;
     constexpr uint32_t idesc_s = idesc_f16(FMT, 128, KT);
-    constexpr uint32_t idesc_o = idesc_f16(FMT, 128, 128);
+    constexpr uint32_t idesc_o = idesc_f16(FMT, 128, D);
     const uint32_t t_sw = tmem + (uint32_t)w * 128u, t_ow = tmem + 256u + (uint32_t)w * 128u;
     const uint64_t da = sw128_desc(q_s + (uint32_t)w * kUmmaQTile);
     // S_w(step in K ring slot ks) = Q_w K^T into S buffer b, then "S_w[b] ready" and "done with the slot"
     auto issue_qk = [&](int b, int ks) {
       const uint64_t db = sw128_desc(k_ring + (uint32_t)ks * kUmmaKVTile);
 #pragma unroll
-      for (int kk = 0; kk < 8; ++kk) {
+      for (int kk = 0; kk < D / 16; ++kk) {
         const uint32_t in_slab = (uint32_t)(kk & 3) * 32u;
         mma_ss(t_sw + (uint32_t)b * 64u, desc_advance(da, (uint32_t)(kk >> 2) * 16384u + in_slab),
                desc_advance(db, (uint32_t)(kk >> 2) * 8192u + in_slab), idesc_s, kk > 0);

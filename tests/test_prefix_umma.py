@@ -28,15 +28,16 @@ def _run(c, path, out=None):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("D", [128, 64])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 @pytest.mark.parametrize("H,KH,BS", [(32, 8, 16), (28, 4, 16), (8, 8, 32), (6, 2, 8), (16, 1, 16), (4, 2, 32),
                                      (3, 1, 16), (10, 2, 16)])
-def test_tcgen05_matches_truth_and_oracle(oracle, dtype, H, KH, BS):
+def test_tcgen05_matches_truth_and_oracle(oracle, dtype, H, KH, BS, D):
     """Ragged batch: no context, contexts that end inside a page / inside a 128-key tile / on a tile edge,
     query lengths below, at and above one 256-row tile, an empty query."""
     ctx = [0, 5, 16, 129, 700, 48, 256]
     ql = [70, 1, 33, 64, 130, 0, 257]
-    c = make_prefix_case(ctx, ql, H, KH, 128, BS, dtype, seed=H + BS, q_pad=8)
+    c = make_prefix_case(ctx, ql, H, KH, D, BS, dtype, seed=H + BS, q_pad=8)
     got = _run(c, "tcgen05")
     assert torch.isfinite(got.float()).all()
     want = _truth_gpu(c)
@@ -48,10 +49,11 @@ def test_tcgen05_matches_truth_and_oracle(oracle, dtype, H, KH, BS):
 
 
 @pytest.mark.gpu
-def test_tcgen05_nan_poisoned_cache_tails():
+@pytest.mark.parametrize("D", [128, 64])
+def test_tcgen05_nan_poisoned_cache_tails(D):
     """Slots past ctx_len in the last context page (and every unused block) hold NaN: they must not
     reach the output through 0 * NaN in P.V."""
-    c = make_prefix_case([3, 77, 130, 1000], [40, 200, 64, 300], 8, 2, 128, 16, torch.float16, seed=9)
+    c = make_prefix_case([3, 77, 130, 1000], [40, 200, 64, 300], 8, 2, D, 16, torch.float16, seed=9)
     BS = 16
     used = set()
     for b, n in enumerate(c["context_lens"].tolist()):
@@ -82,11 +84,12 @@ def test_tcgen05_fuzz(seed):
     B = r.randint(1, 5)
     ctx = [r.choice([0, r.randint(1, 40), r.randint(100, 1500), 128 * r.randint(1, 6)]) for _ in range(B)]
     ql = [r.choice([1, r.randint(2, 40), r.randint(60, 600)]) for _ in range(B)]
-    c = make_prefix_case(ctx, ql, G * KH, KH, 128, BS, dtype, seed=seed, q_pad=r.choice([0, 8]))
+    D = r.choice([64, 128])
+    c = make_prefix_case(ctx, ql, G * KH, KH, D, BS, dtype, seed=seed, q_pad=r.choice([0, 8]))
     got = _run(c, "tcgen05")
     assert torch.isfinite(got.float()).all()
     err = (got.double() - _truth_gpu(c)).abs().max().item()
-    assert err <= TOL[dtype], (seed, BS, G, KH, dtype, ctx, ql, err)
+    assert err <= TOL[dtype], (seed, D, BS, G, KH, dtype, ctx, ql, err)
 
 
 @pytest.mark.gpu
@@ -118,7 +121,7 @@ def test_tcgen05_writes_only_its_rows():
 @pytest.mark.gpu
 def test_tcgen05_rejects_what_it_cannot_run():
     from light_vllm_b200.attention.prefix_prefill import context_attention_fwd
-    c = make_prefix_case([16], [8], 4, 2, 64, 16, torch.float16, seed=1)
+    c = make_prefix_case([16], [8], 4, 2, 96, 16, torch.float16, seed=1)  # head sizes other than 64 / 128
     d = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in c.items()}
     with pytest.raises(RuntimeError, match="tcgen05"):
         _call(functools.partial(context_attention_fwd, path="tcgen05"), d, torch.empty_like(d["query"]))
