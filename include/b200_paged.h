@@ -317,6 +317,14 @@ int b200_ctx_exchange_status(const void* local_buf, int world, int32_t* status, 
 int b200_ctx_exchange_status_async(const void* local_buf, int world, int32_t* pinned_host4, int device,
                                    b200_stream_t stream);
 int b200_ctx_exchange_set_timeout(void* local_buf, int world, int timeout_ms, int device);
+/* Zero-copy failure mirror: 4 pinned (mapped) host words {status, -, -, failing epoch} that the exchange kernel
+ * writes when a wait times out, so that the host can notice at its next call without copying the status word
+ * back every step (NULL detaches). */
+int b200_ctx_exchange_set_host_mirror(void* local_buf, int world, void* pinned_host4, int device);
+/* Diagnostics (synchronises): CTA 0's timestamps of the last two exchange launches, out32[2][8][2] =
+ * (globaltimer ns, SM clock) at {entry, dependency resolved, first statistics loaded, first row folded,
+ * rows published, first pair arrived, merged, end}; slot = epoch & 1. */
+int b200_ctx_exchange_trace(const void* local_buf, int world, uint64_t* out32, int device);
 int b200_ctx_exchange_clear_status(void* local_buf, int world, int device);
 
 /* Peer-visible device memory for the exchange buffers: plain cudaMalloc (zero-filled) exported /

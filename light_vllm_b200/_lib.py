@@ -47,6 +47,8 @@ ABI_SYMBOLS = (
     "b200_ctx_exchange_status",
     "b200_ctx_exchange_status_async",
     "b200_ctx_exchange_set_timeout",
+    "b200_ctx_exchange_set_host_mirror",
+    "b200_ctx_exchange_trace",
     "b200_ctx_exchange_clear_status",
     "b200_peer_alloc",
     "b200_peer_free",
@@ -106,6 +108,8 @@ def _load():
     lib.b200_ctx_exchange_status.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_int32), i32]
     lib.b200_ctx_exchange_status_async.argtypes = [vp, i32, vp, i32, vp]
     lib.b200_ctx_exchange_set_timeout.argtypes = [vp, i32, i32, i32]
+    lib.b200_ctx_exchange_set_host_mirror.argtypes = [vp, i32, vp, i32]
+    lib.b200_ctx_exchange_trace.argtypes = [vp, i32, vp, i32]
     lib.b200_ctx_exchange_clear_status.argtypes = [vp, i32, i32]
     lib.b200_peer_alloc.argtypes = [ctypes.POINTER(vp), i64, i32]
     lib.b200_peer_free.argtypes = [vp, i32]

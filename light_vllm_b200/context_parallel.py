@@ -112,10 +112,12 @@ class ContextShardGroup:
         # True: the epoch lives in the exchange buffer (CUDA-graph capturable); all ranks must agree
         self.device_epoch = True
         self._scratch = {}   # grow-only per (B, H, D, dtype); must pre-exist any CUDA-graph capture
-        # outcome of the previous call, mirrored asynchronously into pinned host memory
+        # failure mirror: 4 pinned host words the exchange kernel itself writes when a wait times out
+        # (zero-copy; no device-to-host copy on the per-step path)
         self._mirror = torch.zeros(4, dtype=torch.int32).pin_memory() if torch.cuda.is_available() \
             else torch.zeros(4, dtype=torch.int32)
-        self._mirror_event = None
+        if torch.cuda.is_available() and own_buf:
+            _check(_lib.lib.b200_ctx_exchange_set_host_mirror(own_buf, world, self._mirror.data_ptr(), device))
 
     # ---- construction ----
     @staticmethod
@@ -177,20 +179,14 @@ class ContextShardGroup:
     def clear_status(self) -> None:
         _check(_lib.lib.b200_ctx_exchange_clear_status(self._own, self.world, self.device))
         self._mirror.zero_()
-        self._mirror_event = None
 
     def check(self, wait: bool = False) -> None:
         """Raise if a previous call timed out waiting for a peer (its output rows were NaN-poisoned
-        by the kernel).  ``wait=False``: only looks at results that have already arrived -- no
-        synchronisation; ``paged_attention`` calls this on entry, so a failure of call n surfaces
-        at call n+1 at the latest.  ``wait=True`` synchronises on the last call first."""
-        ev = self._mirror_event
-        if ev is None or torch.cuda.is_current_stream_capturing():
-            return  # (event queries are not allowed while a stream of this thread is capturing)
+        by the kernel).  The kernel writes the failure into pinned host words itself, so this is a plain
+        host-memory read: ``paged_attention`` calls it on entry and a failure of call n surfaces at the
+        first call after that kernel has run.  ``wait=True`` synchronises the device first."""
         if wait:
-            ev.synchronize()
-        elif not ev.query():
-            return
+            torch.cuda.synchronize(self.device)
         if int(self._mirror[0]) != 0:
             raise RuntimeError(
                 f"context-sharded attention: rank {self.rank} timed out waiting for rank "
@@ -239,9 +235,3 @@ class ContextShardGroup:
             query.device.index if query.device.index is not None else torch.cuda.current_device(),
             torch.cuda.current_stream(query.device).cuda_stream)
         _check(rc)
-        if phases & 2 and not torch.cuda.is_current_stream_capturing():
-            stream = torch.cuda.current_stream(query.device)
-            _check(_lib.lib.b200_ctx_exchange_status_async(self._own, self.world, self._mirror.data_ptr(),
-                                                           self.device, stream.cuda_stream))
-            self._mirror_event = torch.cuda.Event()
-            self._mirror_event.record(stream)

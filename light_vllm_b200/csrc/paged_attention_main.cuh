@@ -63,6 +63,9 @@ __global__ void __launch_bounds__(B200_ATTN_MAXT, B200_ATTN_MINB) paged_attentio
   constexpr int ROWF = D + kMergePad;            // floats per merged row
   static_assert(PAGE_BYTES % 16 == 0, "bulk copies need 16-byte multiples");
 
+  // A kernel queued behind this one with programmatic stream serialisation (the context-sharded exchange
+  // kernel) may become resident now and park in griddepcontrol.wait; a no-op for ordinary successors.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   extern __shared__ __align__(128) unsigned char smem[];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;

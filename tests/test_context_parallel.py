@@ -267,6 +267,33 @@ def test_missing_peer_times_out_instead_of_hanging():
             g.close()
 
 
+@pytest.mark.gpu
+def test_exchange_trace_is_monotonic():
+    """b200_ctx_exchange_trace: CTA 0's eight timestamps of the last exchange launch, in program order."""
+    import ctypes
+    from light_vllm_b200 import _lib
+    from light_vllm_b200.context_parallel import ContextShardGroup
+    case = make_case(2, 8, 2, 128, 16, [700, 90], torch.float16, seed=3)
+    d = to_device(case, "cuda:0")
+    sh = ContextSharding(1, 16, 1)
+    grp = ContextShardGroup.create_local(1, 16, 128, 0)[0]
+    try:
+        bt, ll, mx = sh.shard_batch(case["block_tables"], [700, 90], 0)
+        out = torch.zeros_like(d["query"])
+        for _ in range(2):
+            grp.paged_attention(out, d["query"], d["key_cache"], d["value_cache"], 2, case["scale"], bt.cuda(),
+                                ll.cuda(), 16, mx)
+        buf = (ctypes.c_uint64 * 32)()
+        assert _lib.lib.b200_ctx_exchange_trace(grp._own, 1, buf, 0) == 0
+        for call in range(2):
+            ns = [buf[call * 16 + 2 * i] for i in range(8)]
+            assert ns[0] > 0 and all(b >= a for a, b in zip(ns, ns[1:])), ns
+            assert ns[7] - ns[0] < 1_000_000_000
+        grp.check(wait=True)
+    finally:
+        grp.close()
+
+
 def _ipc_worker(rank, world, port, tmpdir):
     import sys
     here = os.path.dirname(os.path.abspath(__file__))
