@@ -36,69 +36,115 @@ struct CtxShardArgs {
 // ---------------------------------------------------------------------------------------
 // v2 merge: out = sum_j tmp_out_j * exp_sum_j * e^(m_j - m) / (sum_j exp_sum_j e^(m_j - m) + 1e-6)
 // (reference: paged_attention_v2_reduce_kernel, attention_kernels.cu:565-669, one 128-thread CTA
-// per (seq, head)).  Here: also one CTA per (seq, head); the weights go to shared memory, the four
-// warps fold interleaved quarters of the partitions (coalesced 4-byte row loads, four short
-// chains instead of one long one) and the CTA adds the partial rows.
+// per (seq, head)).  Here: also one CTA per (seq, head), launched as a programmatic dependent of the
+// partition pass; statistics and the first rows are requested in one round trip, the four warps fold
+// interleaved quarters of the partitions (coalesced 4-byte row loads, four short chains instead of one
+// long one) and the CTA adds the partial rows.  The same fold runs inside the context-sharded exchange
+// kernel (context_shard.cu).
 // `partition_tokens` is the context length one partition covers (a multiple of 512 chosen by
 // make_plan; the scratch tensors' partition stride stays max_num_partitions).
 // ---------------------------------------------------------------------------------------
+constexpr int kReducePrefetch = 8;  // partitions per warp requested before their weights exist
+
 template <typename T>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 4)  // <= 128 registers: parks beside the partition pass's resident CTAs
 paged_attention_v2_reduce_kernel(T* __restrict__ out, const float* __restrict__ exp_sums,
                                  const float* __restrict__ max_logits,
                                  const T* __restrict__ tmp_out, const int32_t* __restrict__ seq_lens,
                                  int num_heads, int head_size, int max_num_partitions,
-                                 int partition_tokens, int weights_stride, int64_t total_pairs) {
-  // One CTA per (seq, head): all warps derive the weights (shared memory), then the four warps fold
-  // interleaved quarters of the partitions -- independent coalesced row loads, short dependency
-  // chains -- and the CTA adds the four partial rows.
-  extern __shared__ float wsm[];  // [weights_stride] weights + [4][head_size] partial rows
-  float* w = wsm;
-  float* part = wsm + weights_stride;
+                                 int partition_tokens, int parts_cap, int64_t total_pairs) {
+  // One CTA per (seq, head).  Launched with programmatic stream serialisation behind the partition pass
+  // (which triggers its dependents once all of its CTAs run): the grid is resident and parked here when
+  // the partials land.  The first kReducePrefetch rows of every warp, the statistics and seq_lens are then
+  // requested together -- one memory round trip -- and the four warps fold interleaved quarters of the
+  // partitions (independent coalesced row loads, short dependency chains); the CTA adds the four partial rows.
+  extern __shared__ float wsm[];  // [4][head_size] partial rows | [parts_cap] max logits | [parts_cap] exp sums
+  float* part = wsm;
+  float* sm_ml = wsm + 4 * head_size;
+  float* sm_es = sm_ml + parts_cap;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   for (int64_t pair = blockIdx.x; pair < total_pairs; pair += gridDim.x) {
     const int seq = (int)(pair / num_heads);
     const int seq_len = seq_lens[seq];
-    const int np = (seq_len + partition_tokens - 1) / partition_tokens;
     T* o = out + pair * head_size;
     const T* t = tmp_out + pair * max_num_partitions * head_size;
+    const float* ml = max_logits + pair * max_num_partitions;
+    const float* es = exp_sums + pair * max_num_partitions;
+    float pre[kReducePrefetch][2][2];  // [partition warp + 4u][64-wide slice of the first 128 elements][2]
+#pragma unroll
+    for (int u = 0; u < kReducePrefetch; ++u) {
+      const int j = warp + 4 * u;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const int d0 = 2 * lane + 64 * c;
+        // rows below parts_cap exist in the scratch tensor whether or not this sequence filled them: the
+        // guard does not depend on seq_lens (unused rows are dropped by a select, never multiplied by 0)
+        const bool ok = j < parts_cap && d0 < head_size;
+        pre[u][c][0] = ok ? to_f32<T>(t[(int64_t)j * head_size + d0]) : 0.f;
+        pre[u][c][1] = ok ? to_f32<T>(t[(int64_t)j * head_size + d0 + 1]) : 0.f;
+      }
+    }
+    for (int j = threadIdx.x; j < parts_cap; j += blockDim.x) {
+      sm_ml[j] = ml[j];
+      sm_es[j] = es[j];
+    }
+    const int np = min((seq_len + partition_tokens - 1) / partition_tokens, parts_cap);
+    __syncthreads();
     if (np <= 1) {
       // np == 1: plain copy (attention_kernels.cu:582-594).  np == 0 (empty sequence): the
       // partition kernel wrote nothing; define the output as zeros.
       for (int d = threadIdx.x; d < head_size; d += blockDim.x) o[d] = np == 1 ? t[d] : from_f32<T>(0.f);
+      __syncthreads();
       continue;
     }
-    const float* ml = max_logits + pair * max_num_partitions;
-    const float* es = exp_sums + pair * max_num_partitions;
     float mx = -__builtin_huge_valf();
-    for (int j = lane; j < np; j += 32) mx = fmaxf(mx, ml[j]);
+    for (int j = lane; j < np; j += 32) mx = fmaxf(mx, sm_ml[j]);
 #pragma unroll
     for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
     float sum = 0.f;
-    for (int j = lane; j < np; j += 32) {
-      const float r = es[j] * expf(ml[j] - mx);
-      if (warp == 0) w[j] = r;
-      sum += r;
-    }
+    for (int j = lane; j < np; j += 32) sum += sm_es[j] * expf(sm_ml[j] - mx);
 #pragma unroll
     for (int s = 16; s >= 1; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
     const float inv = __fdividef(1.f, sum + 1e-6f);
-    __syncthreads();
-    for (int d0 = 2 * lane; d0 < head_size; d0 += 64) {  // head sizes are even
-      float a0 = 0.f, a1 = 0.f;
-#pragma unroll 4
-      for (int j = warp; j < np; j += 4) {
-        const float wj = w[j];
-        a0 += to_f32<T>(t[(int64_t)j * head_size + d0]) * wj;
-        a1 += to_f32<T>(t[(int64_t)j * head_size + d0 + 1]) * wj;
+    float acc[4][2];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) acc[c][0] = acc[c][1] = 0.f;
+#pragma unroll
+    for (int u = 0; u < kReducePrefetch; ++u) {
+      const int j = warp + 4 * u;
+      const float wj = j < np ? sm_es[j] * expf(sm_ml[j] - mx) : 0.f;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        acc[c][0] += j < np ? pre[u][c][0] * wj : 0.f;
+        acc[c][1] += j < np ? pre[u][c][1] * wj : 0.f;
       }
-      *reinterpret_cast<float2*>(part + warp * head_size + d0) = make_float2(a0, a1);
+    }
+    // whatever the prefetch did not cover: partitions beyond 4 * kReducePrefetch, elements beyond 128
+    if (np > 4 * kReducePrefetch || head_size > 128) {
+      for (int j = warp; j < np; j += 4) {
+        const float wj = sm_es[j] * expf(sm_ml[j] - mx);
+        const bool fetched = j < 4 * kReducePrefetch;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int d0 = 2 * lane + 64 * c;
+          if (d0 < head_size && !(fetched && c < 2)) {
+            acc[c][0] += to_f32<T>(t[(int64_t)j * head_size + d0]) * wj;
+            acc[c][1] += to_f32<T>(t[(int64_t)j * head_size + d0 + 1]) * wj;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int d0 = 2 * lane + 64 * c;
+      if (d0 < head_size) *reinterpret_cast<float2*>(part + warp * head_size + d0) = make_float2(acc[c][0], acc[c][1]);
     }
     __syncthreads();
     for (int d = threadIdx.x; d < head_size; d += blockDim.x)
       o[d] = from_f32<T>((part[d] + part[head_size + d] + part[2 * head_size + d] + part[3 * head_size + d]) * inv);
-    __syncthreads();  // w[] and part[] are reused by the next pair
+    __syncthreads();  // the shared buffers are reused by the next pair
   }
 }
 
@@ -380,25 +426,33 @@ static int run_attention(int version, void* out, float* exp_sums, float* max_log
                                ctx->epoch, ctx->phases, stream);
   if (split_v2) {
     const int64_t pairs = (int64_t)num_seqs * num_heads;
-    const int64_t cap = (int64_t)pl.num_sms * 8;  // grid-stride beyond eight CTAs per SM
+    const int64_t cap = (int64_t)pl.num_sms * 4;  // grid-stride beyond four CTAs per SM
     const unsigned blocks = (unsigned)(pairs < cap ? pairs : cap);
-    const int wstride = (pl.v2_parts + 3) & ~3;
-    const size_t wsmem = ((size_t)wstride + (size_t)4 * head_size) * sizeof(float);
-    if (q_dtype == B200_DT_F16)
-      paged_attention_v2_reduce_kernel<__half><<<blocks, 128, wsmem, stream>>>(
-          static_cast<__half*>(out), exp_sums, max_logits, static_cast<const __half*>(tmp_out),
-          seq_lens, num_heads, head_size, max_num_partitions, pl.v2_partition_tokens, wstride,
-          pairs);
-    else if (q_dtype == B200_DT_F32)
-      paged_attention_v2_reduce_kernel<float><<<blocks, 128, wsmem, stream>>>(
-          static_cast<float*>(out), exp_sums, max_logits, static_cast<const float*>(tmp_out),
-          seq_lens, num_heads, head_size, max_num_partitions, pl.v2_partition_tokens, wstride,
-          pairs);
-    else
-      paged_attention_v2_reduce_kernel<__nv_bfloat16><<<blocks, 128, wsmem, stream>>>(
-          static_cast<__nv_bfloat16*>(out), exp_sums, max_logits,
-          static_cast<const __nv_bfloat16*>(tmp_out), seq_lens, num_heads, head_size,
-          max_num_partitions, pl.v2_partition_tokens, wstride, pairs);
+    const int parts_cap = pl.v2_parts > 1 ? pl.v2_parts : 1;
+    const size_t wsmem = ((size_t)2 * parts_cap + (size_t)4 * head_size) * sizeof(float);
+    B200_CHECK_ARG(head_size <= 256, "paged_attention_v2: the reduce kernel folds rows of up to 256 elements");
+    B200_CHECK_ARG(wsmem <= 48 * 1024, "paged_attention_v2: %d partitions per sequence exceed the reduce kernel's shared memory",
+                   parts_cap);
+    // Programmatic dependent launch: resident and parked in griddepcontrol.wait while the partition pass drains.
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(blocks);
+    cfg.blockDim = dim3(128);
+    cfg.dynamicSmemBytes = wsmem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+#define B200_REDUCE_LAUNCH(T)                                                                               \
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, paged_attention_v2_reduce_kernel<T>, static_cast<T*>(out),          \
+                                  (const float*)exp_sums, (const float*)max_logits,                        \
+                                  static_cast<const T*>(tmp_out), seq_lens, num_heads, head_size,          \
+                                  max_num_partitions, pl.v2_partition_tokens, parts_cap, pairs))
+    if (q_dtype == B200_DT_F16) B200_REDUCE_LAUNCH(__half);
+    else if (q_dtype == B200_DT_F32) B200_REDUCE_LAUNCH(float);
+    else B200_REDUCE_LAUNCH(__nv_bfloat16);
+#undef B200_REDUCE_LAUNCH
     count_launch();
     B200_CUDA_OK(cudaGetLastError());
   }
