@@ -110,6 +110,31 @@ int b200_paged_attention_v2(void* out, float* exp_sums, float* max_logits, void*
                             b200_stream_t stream);
 
 /*
+ * paged_attention_v2_static — NO counterpart in the reference.
+ *   b200_paged_attention_v2 for callers that may not allocate (CUDA graph capture, tight serving loops,
+ *   harnesses that forbid cudaMalloc): the caller passes inputs and `out` only; exp_sums / max_logits /
+ *   tmp_out live in ONE library-owned static device array of B200_STATIC_SCRATCH_BYTES (16 MiB) that every GPU
+ *   loading the library holds until exit.  Calls no cudaMalloc / cudaFree / allocating routine.
+ *   Limit: 2 * align256(4 * cells) + cells * head_size * sizeof(T) <= B200_STATIC_SCRATCH_BYTES with
+ *   cells = num_seqs * num_heads * ceil(max_seq_len / 512); larger calls are rejected (B200_ERR_INVALID, message
+ *   names the sizes) -- use b200_paged_attention_v2 with caller scratch for those.
+ *   Every call on a device shares the array and it keeps the last call's contents (nothing in it needs to
+ *   start at zero, so nothing is cleared): calls that overlap on the GPU (different streams) RACE on it.
+ *   The array's device address is resolved once per device at the first call (cudaGetSymbolAddress); make
+ *   that first call outside stream capture.
+ */
+#define B200_STATIC_SCRATCH_BYTES (16 * 1024 * 1024)
+int b200_paged_attention_v2_static(void* out, const void* query, const void* key_cache,
+                                   const void* value_cache, const int32_t* block_tables,
+                                   const int32_t* seq_lens, const float* alibi_slopes, int num_seqs,
+                                   int num_heads, int num_kv_heads, int head_size, int block_size,
+                                   int max_seq_len, int max_num_blocks_per_seq, int64_t q_stride,
+                                   int64_t kv_block_stride, int64_t kv_head_stride, float scale,
+                                   float k_scale, float v_scale, int q_dtype, int kv_dtype,
+                                   const b200_blocksparse_t* blocksparse, int device,
+                                   b200_stream_t stream);
+
+/*
  * reshape_and_cache — replaces torch.ops._C_cache_ops.reshape_and_cache
  *   (csrc/torch_bindings.cpp:241-247, csrc/cache_kernels.cu:263-289, kernel :152-204).
  *   key/value [num_tokens, num_heads, head_size] T with token strides key_stride/value_stride;

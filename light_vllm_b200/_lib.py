@@ -28,6 +28,7 @@ ABI_SYMBOLS = (
     "b200_parse_kv_cache_dtype",
     "b200_paged_attention_v1",
     "b200_paged_attention_v2",
+    "b200_paged_attention_v2_static",
     "b200_reshape_and_cache",
     "b200_reshape_and_cache_flash",
     "b200_copy_blocks",
@@ -99,6 +100,10 @@ def _load():
     lib.b200_paged_attention_tuned.argtypes = (
         [i32] + [vp] * 10 + [i32] * 8 + [i64] * 3 + [f32] * 3 + [i32] * 2 +
         [vp, ctypes.POINTER(AttnTuning), i32, vp])
+    # out, query, key_cache, value_cache, block_tables, seq_lens, alibi | 7 ints | 3 strides | 3 floats |
+    # q_dtype, kv_dtype | blocksparse | device | stream
+    lib.b200_paged_attention_v2_static.argtypes = (
+        [vp] * 7 + [i32] * 7 + [i64] * 3 + [ctypes.c_float] * 3 + [i32, i32, vp, i32, vp])
     lib.b200_swap_blocks_mode.argtypes = [vp, vp, vp, i32, i64, i32, i32, i32, vp]
     lib.b200_context_attention_fwd.argtypes = (
         [vp] * 10 + [i32] * 7 + [i64] * 12 + [vp, i32, f32, vp, i64, i64, i32, i32, vp])

@@ -1,6 +1,7 @@
 // C entry points for paged attention: argument validation, launch planning, dispatch to the
 // instantiated kernels, and the v2 partition-merge kernel
 // (replaces attention_kernels.cu:565-669, 690-770, 808-829, 848-934, 973-997).
+#include <mutex>
 #include "paged_attention.cuh"
 
 #include <atomic>
@@ -498,6 +499,77 @@ extern "C" int b200_paged_attention_v2(void* out, float* exp_sums, float* max_lo
                        max_num_partitions, q_stride, kv_block_stride, kv_head_stride, scale,
                        k_scale, v_scale, q_dtype, kv_dtype, blocksparse, device,
                        (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------
+// paged_attention_v2 without caller scratch and without any allocation (no counterpart in the reference;
+// added for callers that may not allocate: code under CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).
+// The partition scratch (exp_sums | max_logits | tmp_out) lives in ONE file-scope device array of
+// B200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.  Every call on a device
+// shares it and it keeps the last call's contents: nothing in it has to start at zero (the partition pass
+// writes every (pair, partition) cell the reduce kernel weights; cells it only prefetches are dropped by a
+// select), so nothing is cleared -- but two calls that overlap on the GPU (different streams) race on it.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[B200_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_scratch_mu;
+void* g_static_scratch_ptr[kMaxDevices] = {};  // device address of g_static_scratch per device (set-up cache)
+
+// In host code `g_static_scratch` is a host-side stand-in, not a device address: resolve it once per device,
+// with that device current.
+int static_scratch_address(int dev, unsigned char** ptr) {
+  B200_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "paged_attention_v2_static: device %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    B200_CUDA_OK(cudaGetSymbolAddress(&p, g_static_scratch));
+    B200_CHECK_ARG(p != nullptr && (reinterpret_cast<uintptr_t>(p) & 255) == 0,
+                   "paged_attention_v2_static: bad scratch address");
+    g_static_scratch_ptr[dev] = p;
+  }
+  *ptr = static_cast<unsigned char*>(g_static_scratch_ptr[dev]);
+  return B200_OK;
+}
+}  // namespace
+
+extern "C" int b200_paged_attention_v2_static(
+    void* out, const void* query, const void* key_cache, const void* value_cache,
+    const int32_t* block_tables, const int32_t* seq_lens, const float* alibi_slopes, int num_seqs,
+    int num_heads, int num_kv_heads, int head_size, int block_size, int max_seq_len,
+    int max_num_blocks_per_seq, int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    float scale, float k_scale, float v_scale, int q_dtype, int kv_dtype,
+    const b200_blocksparse_t* blocksparse, int device, b200_stream_t stream) {
+  B200_CHECK_ARG(num_seqs >= 0 && num_heads > 0 && head_size > 0 && max_seq_len >= 0,
+                 "paged_attention_v2_static: bad sizes");
+  if (num_seqs == 0) return B200_OK;
+  const int64_t parts = max_seq_len > 0 ? (max_seq_len + kPartitionSize - 1) / kPartitionSize : 1;
+  const int64_t cells = (int64_t)num_seqs * num_heads * parts;
+  const int64_t elem = q_dtype == B200_DT_F32 ? 4 : 2;
+  const int64_t stat_bytes = (cells * 4 + 255) & ~(int64_t)255;  // exp_sums, max_logits: 256-byte aligned sections
+  const int64_t need = 2 * stat_bytes + cells * head_size * elem;
+  B200_CHECK_ARG(need <= (int64_t)B200_STATIC_SCRATCH_BYTES,
+                 "paged_attention_v2_static: %d seqs x %d heads x %d partitions x head size %d needs %lld scratch "
+                 "bytes, the built-in array holds %lld (use b200_paged_attention_v2 with caller scratch)",
+                 num_seqs, num_heads, (int)parts, head_size, (long long)need,
+                 (long long)B200_STATIC_SCRATCH_BYTES);
+  DeviceGuard guard(device);
+  B200_CUDA_OK(guard.err);
+  int dev = device;
+  if (dev < 0) B200_CUDA_OK(cudaGetDevice(&dev));
+  unsigned char* base = nullptr;
+  int rc = static_scratch_address(dev, &base);
+  if (rc != B200_OK) return rc;
+  float* exp_sums = reinterpret_cast<float*>(base);
+  float* max_logits = reinterpret_cast<float*>(base + stat_bytes);
+  void* tmp_out = base + 2 * stat_bytes;
+  return run_attention(2, out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
+                       block_tables, seq_lens, alibi_slopes, num_seqs, num_heads, num_kv_heads,
+                       head_size, block_size, max_seq_len, max_num_blocks_per_seq, (int)parts, q_stride,
+                       kv_block_stride, kv_head_stride, scale, k_scale, v_scale, q_dtype, kv_dtype,
+                       blocksparse, dev, (cudaStream_t)stream);
 }
 
 extern "C" int b200_paged_attention_ctx_shard(
