@@ -235,8 +235,37 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
   }
   long long base = (long long)num_seqs * num_kv_heads * pl.gchunks;  // CTAs before any split
   if (base < 1) base = 1;
+  // One-wave regime (profiles/r2_small_plan_sweep.md): when the unsplit grid has at most one CTA per SM, the
+  // batch-oriented plan below (4-warp CTAs, three per SM, split -- and for B <= 2 head-split -- until the slots
+  // are full) pays 2-3 prologues and a cluster / scratch merge per SM inside a kernel that lasts one wave, and
+  // the head split multiplies the L2 traffic.  Measured better on every such shape: ONE 8-warp CTA per SM (twice
+  // the pages in flight per CTA), no head split, context split only while the grid stays within the SM count;
+  // 2 stages when most SMs have a CTA, 3 when fewer do.  v1: cluster 8 at one CTA per SM co-schedules fewer
+  // than 16 clusters (two per GPC at best), so it is used up to half the SMs only.  v2 runs unsplit from a
+  // third of the SMs up, which also drops its reduce launch.
+  // v1 1 x 8192: 15.7 -> 12.6 us, 1 x 32768: 45.2 -> 27.8 us, 16 x 2048: 25.6 -> 23.2 us, 16 x 4096: 45.0 -> 42.2 us
+  // (0.97 of the HBM peak); v2 16 x 2048: 27.3 -> 23.1 us.
+  int wide_split = 0;
+  if (kn.warps <= 0 && kn.stages <= 0 && kn.cluster <= 0 && kn.rows <= 0 && q_dtype != B200_DT_F32 &&
+      base <= num_sms && e.smem(8, 2) <= (size_t)227 * 1024) {  // (head 256 x block 32: an 8-warp ring does not fit)
+    const int pages = (max_seq_len + block_size - 1) / block_size;
+    int sp = 1;
+    if (version == 1) {
+      auto cap = [&](int c) { return c >= 8 ? num_sms / 2 : (c >= 4 ? num_sms * 9 / 10 : num_sms); };
+      while (sp < 8 && base * sp * 2 <= cap(sp * 2) && pages / (2 * sp) >= 2 * 8) sp *= 2;
+    } else if (base * 3 < num_sms) {
+      sp = (int)(num_sms / base);  // partitions: as many as keep the grid within one CTA per SM
+      const int most = pages / (kPartitionSize / block_size > 0 ? kPartitionSize / block_size : 1);
+      if (sp > most) sp = most;
+      if (sp < 1) sp = 1;
+    }
+    wide_split = sp;
+    pl.nwarps = 8;
+  }
   int ns = kn.stages;
-  if (ns <= 0) {
+  if (wide_split > 0) {
+    ns = base * wide_split * 4 >= 3LL * num_sms ? 2 : 3;
+  } else if (ns <= 0) {
     // candidate A: ring that lets three CTAs share an SM (2..4 stages); candidate B: a deeper ring
     // with two CTAs per SM.  A wins whenever the grid runs for many waves or fits in one; B wins
     // when a 1-3 wave grid would leave A with a nearly empty last wave (c2: 512 CTAs on 444 slots).
@@ -291,7 +320,7 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
   const long long finest = version == 1 ? (q_dtype == B200_DT_F32 ? 1 : 8) : parts_max;
   // (measured, profiles/r2_sweep_small.md: the head split pays for v1 -- one launch, B = 1 x 8 Ki tokens 23.9 ->
   // 18.6 us -- and changes nothing for v2, whose two launches set the floor at these sizes)
-  if (kn.rows <= 0 && q_dtype != B200_DT_F32 && version == 1) {
+  if (kn.rows <= 0 && q_dtype != B200_DT_F32 && version == 1 && wide_split == 0) {
     while (pl.rows > 1 && 2 * base * finest <= slots) {  // less than half the slots even at the finest split
       pl.rows = (pl.rows + 1) / 2;
       pl.gchunks = (group + pl.rows - 1) / pl.rows;
@@ -305,6 +334,8 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
       pl.cluster = 1;  // the fp32 kernel has no cluster merge: v1 runs unsplit
     } else if (forced > 0) {
       pl.cluster = forced;
+    } else if (wide_split > 0) {
+      pl.cluster = wide_split;
     } else {
       pl.cluster = v1_split(base);
     }
@@ -312,6 +343,8 @@ static int make_plan(Plan& pl, int version, int num_seqs, int num_heads, int num
     int parts;
     if (kn.cluster > 0) {  // tuning: "split" = forced partition count for v2
       parts = kn.cluster < parts_max ? kn.cluster : parts_max;
+    } else if (wide_split > 0) {
+      parts = wide_split < parts_max ? wide_split : parts_max;
     } else {
       // Measured (profiles/r2_sweep_small.md, tools/sweep_ctx_plan.sh): for grids that need a split at all
       // the best partition count puts ~1.5 CTAs on every SM in ONE resident wave (4 x 16 Ki tokens: 7

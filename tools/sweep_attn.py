@@ -28,6 +28,8 @@ def main():
     ap.add_argument("--version", type=int, default=0)
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--ctx", type=int, default=0)
+    ap.add_argument("--graph", type=int, default=0,
+                    help="also time the calls issued N per CUDA graph (no host / launch-API time): graph_us")
     args = ap.parse_args()
     from light_vllm_b200 import _custom_ops as ops
     from light_vllm_b200 import _lib
@@ -94,15 +96,43 @@ def main():
         torch.cuda.synchronize()
         return e0.elapsed_time(e1) / args.reps * 1e3
 
+    def time_graph(mod, call, n):
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            call(mod, 0)
+            side.synchronize()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=side):
+                for i in range(n):
+                    call(mod, i % L)
+        torch.cuda.current_stream().wait_stream(side)
+        reps = max(3, args.reps // n)
+        for _ in range(2):
+            gr.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            gr.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps / n * 1e3
+
     ab = algorithmic_bytes_attention(c)
     for plan in args.plans.split(";"):
         tn = tuple(int(x) for x in plan.split(","))  # warps,stages,split[,head_rows]
         try:
             us = time_it(ops, tuned_call(tn))
             info = _lib.attention_plan(c["version"], B, H, KH, D, BS, ctx, dtype, kv, 0, tn)
-            print(json.dumps({"impl": "b200", "config": args.config, "v": c["version"], "B": B,
-                              "ctx": ctx, "plan": plan, "us": round(us, 2),
-                              "GBps": round(ab / us / 1e3, 1), "resolved": info}), flush=True)
+            row = {"impl": "b200", "config": args.config, "v": c["version"], "B": B,
+                   "ctx": ctx, "plan": plan, "us": round(us, 2),
+                   "GBps": round(ab / us / 1e3, 1), "resolved": info}
+            if args.graph:
+                gus = time_graph(ops, tuned_call(tn), args.graph)
+                row["graph_us"] = round(gus, 2)
+                row["graph_GBps"] = round(ab / gus / 1e3, 1)
+            print(json.dumps(row), flush=True)
         except RuntimeError as e:
             print(json.dumps({"impl": "b200", "plan": plan, "error": str(e)[:200]}), flush=True)
     if args.ref:
