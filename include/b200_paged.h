@@ -285,7 +285,8 @@ int b200_context_attention_fwd(
  * 16-byte aligned q / out rows -- B200_ERR_UNSUPPORTED otherwise). */
 #define B200_PREFIX_PATH_AUTO 0
 #define B200_PREFIX_PATH_MMA_SYNC 1
-#define B200_PREFIX_PATH_TCGEN05 2
+#define B200_PREFIX_PATH_TCGEN05 2        /* tcgen05 tile loop; K/V tiles by TMA tensor copies when block size is 16 */
+#define B200_PREFIX_PATH_TCGEN05_GATHER 3 /* tcgen05 tile loop with the per-thread 16-byte gather (any block size) */
 int b200_context_attention_fwd_path(
     const void* q, const void* k, const void* v, void* out, const void* key_cache,
     const void* value_cache, const int32_t* block_tables, const int32_t* start_loc,

@@ -137,7 +137,7 @@ def last_error() -> str:
     return lib.b200_last_error().decode()
 
 
-PREFIX_PATHS = {"auto": 0, "mma_sync": 1, "tcgen05": 2}  # B200_PREFIX_PATH_*
+PREFIX_PATHS = {"auto": 0, "mma_sync": 1, "tcgen05": 2, "tcgen05_gather": 3}  # B200_PREFIX_PATH_*
 _DT = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
 
 

@@ -17,7 +17,11 @@
 #include "prefix_prefill.cuh"
 #include "prefix_prefill_umma.cuh"
 
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
 #include <atomic>
+#include <cstring>
 
 namespace b200 {
 
@@ -623,14 +627,62 @@ bool umma_eligible(const PrefixParams& p) {
          p.o_s1 % 8 == 0;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (no link against libcuda).
+PFN_cuTensorMapEncodeTiled tensor_map_encoder() {
+  static std::atomic<void*> cached{nullptr};
+  void* fn = cached.load(std::memory_order_acquire);
+  if (fn == nullptr) {
+    cudaDriverEntryPointQueryResult st;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &st) != cudaSuccess ||
+        st != cudaDriverEntryPointSuccess)
+      return nullptr;
+    cached.store(fn, std::memory_order_release);
+  }
+  return reinterpret_cast<PFN_cuTensorMapEncodeTiled>(fn);
+}
+
+// Tensor maps of the TMA-fed tile loop (16-bit elements, block size 16).  A K page is [D/8][BS][8]: dim0 = the
+// BS * 8 contiguous elements of one chunk, dim1 = chunk; the box is 8 tokens x all chunks, no swizzle.  A V page is
+// [D][BS]: dim0 = token, dim1 = d; the box is the page, SWIZZLE_32B.  dim2 = kv head, dim3 = block (cache) or
+// staged slice (scratch: slices of [K page | V page] per kv head).  Block ids come from the block table and are
+// not range-checked by the copy engine: dim3 is declared as large as the format allows.
+template <int D, int BS>
+bool encode_prefix_maps(const PrefixParams& p, bool bf16, PrefixTmaMaps& m) {
+  PFN_cuTensorMapEncodeTiled enc = tensor_map_encoder();
+  if (enc == nullptr) return false;
+  const CUtensorMapDataType dt = bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  const cuuint32_t ones[4] = {1, 1, 1, 1};
+  const cuuint64_t many = (cuuint64_t)1 << 31;
+  const cuuint64_t slice_bytes = (cuuint64_t)2 * D * BS * 2;
+  auto make = [&](unsigned char* out, const void* base, bool is_k, cuuint64_t head_bytes, cuuint64_t blk_bytes) {
+    const cuuint64_t dims[4] = {is_k ? (cuuint64_t)BS * 8 : (cuuint64_t)BS, is_k ? (cuuint64_t)D / 8 : (cuuint64_t)D,
+                                (cuuint64_t)p.num_kv_heads, many};
+    const cuuint64_t strides[3] = {is_k ? (cuuint64_t)BS * 16 : (cuuint64_t)BS * 2, head_bytes, blk_bytes};
+    const cuuint32_t box[4] = {is_k ? 64u : (cuuint32_t)BS, is_k ? (cuuint32_t)D / 8 : (cuuint32_t)D, 1, 1};
+    return enc(reinterpret_cast<CUtensorMap*>(out), dt, 4, const_cast<void*>(base), dims, strides, box, ones,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, is_k ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_32B,
+               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  };
+  return make(m.k, p.k_cache, true, (cuuint64_t)p.kc_hs * 2, (cuuint64_t)p.kc_bs * 2) &&
+         make(m.v, p.v_cache, false, (cuuint64_t)p.vc_hs * 2, (cuuint64_t)p.vc_bs * 2) &&
+         make(m.sk, p.kv_scratch, true, slice_bytes, slice_bytes * p.num_kv_heads) &&
+         make(m.sv, p.kv_scratch + (size_t)D * BS * 2, false, slice_bytes, slice_bytes * p.num_kv_heads);
+}
+
+// `gather_only`: keep the per-thread LDGSTS gather (B200_PREFIX_PATH_TCGEN05_GATHER; also what block sizes other
+// than 16, caches whose strides are not 16-byte multiples and drivers without the encoder entry point get).
 template <typename T, int D, int BS>
-int launch_prefix_umma(PrefixParams& p, int num_seqs, int max_query_len, int device, cudaStream_t stream) {
+int launch_prefix_umma(PrefixParams& p, int num_seqs, int max_query_len, int device, cudaStream_t stream,
+                       bool gather_only) {
   p.tok_tile = kUmmaRows / p.group;
-  auto kern = context_attention_umma_kernel<T, D, BS>;
   static std::atomic<int> configured[64];
   const int slot = device & 63;
   if (!configured[slot].load(std::memory_order_acquire)) {
-    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUmmaSmem));
+    B200_CUDA_OK(cudaFuncSetAttribute(context_attention_umma_kernel<T, D, BS, false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUmmaSmem));
+    if constexpr (BS == 16)
+      B200_CUDA_OK(cudaFuncSetAttribute(context_attention_umma_kernel<T, D, BS, true>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUmmaSmem));
     configured[slot].store(1, std::memory_order_release);
   }
   const int rc = launch_prefix_stage<T, D, BS>(p, num_seqs, max_query_len, stream);
@@ -638,7 +690,19 @@ int launch_prefix_umma(PrefixParams& p, int num_seqs, int max_query_len, int dev
   const int tiles = (max_query_len + p.tok_tile - 1) / p.tok_tile;
   B200_CHECK_ARG(p.num_kv_heads <= 65535 && num_seqs <= 65535, "context_attention_fwd: grid too large");
   dim3 grid(tiles, p.num_kv_heads, num_seqs);
-  kern<<<grid, kUmmaThreads, kUmmaSmem, stream>>>(p);
+  PrefixTmaMaps maps;
+  bool tma = false;
+  if constexpr (BS == 16) {
+    auto a16 = [](const void* ptr) { return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0; };
+    tma = !gather_only && a16(p.k_cache) && a16(p.v_cache) && p.kc_hs % 8 == 0 && p.kc_bs % 8 == 0 &&
+          p.vc_hs % 8 == 0 && p.vc_bs % 8 == 0 &&
+          encode_prefix_maps<D, BS>(p, std::is_same<T, __nv_bfloat16>::value, maps);
+    if (tma) context_attention_umma_kernel<T, D, BS, true><<<grid, kUmmaThreads, kUmmaSmem, stream>>>(p, maps);
+  }
+  if (!tma) {
+    memset(&maps, 0, sizeof(maps));
+    context_attention_umma_kernel<T, D, BS, false><<<grid, kUmmaThreads, kUmmaSmem, stream>>>(p, maps);
+  }
   count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200_OK;
@@ -648,16 +712,17 @@ template <typename T, int D, int BS>
 int launch_prefix(PrefixParams& p, int num_seqs, int max_query_len, int device, cudaStream_t stream, int path) {
   if constexpr (D == 128 || D == 64) {
     const bool can = umma_eligible<D>(p);
-    if (path == B200_PREFIX_PATH_TCGEN05 && !can) {
+    const bool forced = path == B200_PREFIX_PATH_TCGEN05 || path == B200_PREFIX_PATH_TCGEN05_GATHER;
+    if (forced && !can) {
       set_error("context_attention_fwd: the tcgen05 path needs head size 64 or 128, no ALiBi / sliding window, "
                 "a staging scratch and 16-byte aligned q / out rows");
       return B200_ERR_UNSUPPORTED;
     }
     // auto: the 256-row tile pays once a sequence brings at least one full M tile of rows
-    if (can && (path == B200_PREFIX_PATH_TCGEN05 ||
-                (path == B200_PREFIX_PATH_AUTO && (int64_t)max_query_len * p.group >= 128)))
-      return launch_prefix_umma<T, D, BS>(p, num_seqs, max_query_len, device, stream);
-  } else if (path == B200_PREFIX_PATH_TCGEN05) {
+    if (can && (forced || (path == B200_PREFIX_PATH_AUTO && (int64_t)max_query_len * p.group >= 128)))
+      return launch_prefix_umma<T, D, BS>(p, num_seqs, max_query_len, device, stream,
+                                          path == B200_PREFIX_PATH_TCGEN05_GATHER);
+  } else if (path == B200_PREFIX_PATH_TCGEN05 || path == B200_PREFIX_PATH_TCGEN05_GATHER) {
     set_error("context_attention_fwd: the tcgen05 path needs head size 64 or 128 (got %d)", D);
     return B200_ERR_UNSUPPORTED;
   }
@@ -740,7 +805,7 @@ extern "C" int b200_context_attention_fwd_path(
     float scale, void* kv_scratch, int64_t kv_scratch_bytes, int64_t num_tokens, int dtype,
     int device, b200_stream_t stream, int path) {
   B200_CHECK_ARG(path == B200_PREFIX_PATH_AUTO || path == B200_PREFIX_PATH_MMA_SYNC ||
-                     path == B200_PREFIX_PATH_TCGEN05,
+                     path == B200_PREFIX_PATH_TCGEN05 || path == B200_PREFIX_PATH_TCGEN05_GATHER,
                  "context_attention_fwd: unknown path %d", path);
   B200_CHECK_ARG(num_seqs >= 0 && max_query_len >= 0 && head_size > 0 && block_size > 0,
                  "context_attention_fwd: bad sizes");
@@ -785,7 +850,7 @@ extern "C" int b200_context_attention_fwd_path(
                      ? static_cast<const unsigned char*>(kv_scratch)
                      : nullptr;
   p.scratch_slices = p.kv_scratch ? kv_scratch_bytes / ((int64_t)num_kv_heads * 2 * head_size * block_size * 2) : 0;
-  if (dtype == B200_DT_F32 && path == B200_PREFIX_PATH_TCGEN05) {
+  if (dtype == B200_DT_F32 && (path == B200_PREFIX_PATH_TCGEN05 || path == B200_PREFIX_PATH_TCGEN05_GATHER)) {
     set_error("context_attention_fwd: the tcgen05 path runs fp16 / bf16 only");
     return B200_ERR_UNSUPPORTED;
   }

@@ -20,4 +20,10 @@ struct PrefixParams {
   float scale_log2;
 };
 
+// Four CUtensorMap objects (opaque, 128 bytes, 64-byte aligned) for the TMA-fed tcgen05 tile loop: K and V of the
+// cache, K and V halves of the staged new-token slices.  Encoded on the host per call (prefix_prefill.cu).
+struct alignas(64) PrefixTmaMaps {
+  unsigned char k[128], v[128], sk[128], sv[128];
+};
+
 }  // namespace b200

@@ -50,12 +50,12 @@ constexpr int kUmmaKeys = 64;           // keys per step
 constexpr uint32_t kUmmaQTile = 32768;  // bytes of one 128-row x 128-d Q tile
 constexpr uint32_t kUmmaKVTile = 16384; // bytes of one 64-key K (or V) tile
 constexpr int kUmmaKStages = 5, kUmmaVStages = 4;
-constexpr uint32_t kUmmaBarBytes = 8 * (2 * kUmmaKStages + 2 * kUmmaVStages + 4 + 4 + 2) + 16;
+constexpr uint32_t kUmmaBarBytes = 8 * (2 * kUmmaKStages + 2 * kUmmaVStages + 4 + 4 + 2) + 32;
 constexpr uint32_t kUmmaSmem = 2 * kUmmaQTile + (kUmmaKStages + kUmmaVStages) * kUmmaKVTile + kUmmaBarBytes + 1024;
 
-template <typename T, int D, int BS>
+template <typename T, int D, int BS, bool TMA>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
-context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
+context_attention_umma_kernel(const __grid_constant__ PrefixParams p, const __grid_constant__ PrefixTmaMaps maps) {
   using namespace umma;
   static_assert(D == 64 || D == 128, "head size 64 or 128");
   constexpr int KT = kUmmaKeys;
@@ -96,17 +96,19 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
                  bars = v_ring + kUmmaVStages * kUmmaKVTile;
   const uint32_t k_full = bars, k_empty = k_full + 8 * kUmmaKStages, v_full = k_empty + 8 * kUmmaKStages,
                  v_empty = v_full + 8 * kUmmaVStages, s_full = v_empty + 8 * kUmmaVStages,  // [w][buffer]
-                 p_full = s_full + 32, o_ready = p_full + 32, slot = o_ready + 16;  // p_full: [w][buffer]
+                 p_full = s_full + 32, o_ready = p_full + 32, slot = o_ready + 16,  // p_full: [w][buffer]
+                 aux = slot + 8;  // TMA variant: landing barrier of V pages that need patching
 
   if (tid == 0) {
     for (int i = 0; i < kUmmaKStages; ++i) {
-      mbar_init(k_full + 8 * i, 128);
+      mbar_init(k_full + 8 * i, TMA ? 1 : 128);
       mbar_init(k_empty + 8 * i, nq);
     }
     for (int i = 0; i < kUmmaVStages; ++i) {
-      mbar_init(v_full + 8 * i, 128);
+      mbar_init(v_full + 8 * i, TMA ? 1 : 128);
       mbar_init(v_empty + 8 * i, nq);
     }
+    mbar_init(aux, 1);
     for (int i = 0; i < 4; ++i) {
       mbar_init(s_full + 8 * i, 1);
       mbar_init(p_full + 8 * i, 128);
@@ -272,6 +274,111 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
         }
       }
     }
+  } else if (TMA && warp < 12) {
+    // ======================= TMA producer (warp 8): pages -> operand tiles, no per-thread copies =======================
+    // BS = 16.  A K page [D/8][16][8] is fetched as two boxes of 8 tokens x D: each lands as [chunk][8 tokens][16 B],
+    // the canonical NO-swizzle K-major layout (core matrix = 8 keys x 16 bytes; next chunk +128 B, next 8 keys
+    // +16 D bytes).  A V page [D][16] is fetched as ONE box with SWIZZLE_32B: the canonical 32-byte-swizzle K-major
+    // layout of V^T for one 16-key k-step.  Twelve tensor copies replace the 4096 16-byte LDGSTS of a tile, whose
+    // time in flight backed up the MIO queue the softmax warps' MUFU go through (910 -> ~1040 TFLOP/s).
+    // Lanes 0-3 each own one page of the tile.  Keys past the end of the context / the new tokens: K may hold
+    // anything (S is masked before the row maximum), V must be finite there because 0 * NaN is not 0 -- such tiles
+    // (at most two per CTA) take the slow road: land on `aux`, clear by hand, then signal.
+    if constexpr (TMA) {
+      if (warp == 8) {
+        static_assert(!TMA || BS == 16, "one page = one 16-key k-step");
+        constexpr uint32_t KGRP = (uint32_t)D * 16u;       // bytes of 8 keys of K
+        constexpr uint32_t VPAGE = (uint32_t)D * BS * 2u;  // bytes of one V page tile
+        const int32_t* bt = p.block_tables + (int64_t)seq * p.max_blocks_per_seq;
+        const int slice0 = (int)(start / BS) + seq;  // first staged slice of this sequence (guarded above)
+        const bool owner = lane < KT / BS;
+        int ks = 0, kround = 0, vs = 0, vround = 0;
+        uint32_t aux_phase = 0;
+        if (lane == 0) {
+          tma_prefetch_desc(maps.k);
+          tma_prefetch_desc(maps.v);
+        }
+        for (int j = 0; j < nt; ++j) {
+          const bool is_ctx = j < n_ctx_tiles;
+          const int pos = KT * (is_ctx ? j : j - n_ctx_tiles) + BS * lane;  // first key of my page
+          const int nval = owner ? min(BS, max(0, (is_ctx ? ctx : qlen) - pos)) : 0;
+          int c3 = 0;
+          if (nval > 0) c3 = is_ctx ? bt[pos / BS] : slice0 + pos / BS;
+          const void* kmap = is_ctx ? (const void*)maps.k : (const void*)maps.sk;
+          const void* vmap = is_ctx ? (const void*)maps.v : (const void*)maps.sv;
+          const uint32_t have = __ballot_sync(FULL, nval > 0);
+          const bool special = __any_sync(FULL, owner && nval < BS);
+          const uint32_t npages = (uint32_t)__popc(have);
+          {
+            if (kround > 0) mbar_wait_wd(k_empty + 8 * ks, (uint32_t)((kround - 1) & 1));
+            const uint32_t dst = k_ring + (uint32_t)ks * kUmmaKVTile + (uint32_t)(2 * lane) * KGRP;
+            if (lane == 0) mbar_arrive_expect_tx(k_full + 8 * ks, npages * 2u * KGRP);
+            __syncwarp();
+            if (nval > 0) {
+              tma_load_4d(dst, kmap, 0, 0, kvh, c3, k_full + 8 * ks);
+              tma_load_4d(dst + KGRP, kmap, 64, 0, kvh, c3, k_full + 8 * ks);
+            }
+            if (++ks == kUmmaKStages) {
+              ks = 0;
+              ++kround;
+            }
+          }
+          {
+            if (vround > 0) mbar_wait_wd(v_empty + 8 * vs, (uint32_t)((vround - 1) & 1));
+            const uint32_t tile = v_ring + (uint32_t)vs * kUmmaKVTile;
+            if (!special) {
+              if (lane == 0) mbar_arrive_expect_tx(v_full + 8 * vs, npages * VPAGE);
+              __syncwarp();
+              if (nval > 0) tma_load_4d(tile + (uint32_t)lane * VPAGE, vmap, 0, 0, kvh, c3, v_full + 8 * vs);
+            } else {
+              if (npages > 0) {
+                if (lane == 0) mbar_arrive_expect_tx(aux, npages * VPAGE);
+                __syncwarp();
+                if (nval > 0) tma_load_4d(tile + (uint32_t)lane * VPAGE, vmap, 0, 0, kvh, c3, aux);
+                mbar_wait_wd(aux, aux_phase);
+                aux_phase ^= 1u;
+              }
+              for (int pg = 0; pg < KT / BS; ++pg) {
+                const int nv = __shfl_sync(FULL, nval, pg);
+                const uint32_t page = tile + (uint32_t)pg * VPAGE;
+                if (nv == 0) {  // no such page: whatever the slot held (nothing yet, perhaps) must not reach P.V
+                  for (uint32_t o = (uint32_t)lane * 16u; o < VPAGE; o += 512u)
+                    asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(page + o), "r"(0u) : "memory");
+                } else if (nv < BS && is_ctx) {
+                  // last context page: slots past ctx_len may hold anything; row d is 32 bytes whose 16-byte halves
+                  // are swapped when (d >> 2) & 1 (SWIZZLE_32B).  Staged new-token pages are zero filled already.
+                  for (int d = lane; d < D; d += 32) {
+                    const uint32_t row = page + (uint32_t)d * 32u;
+                    const int sw = (d >> 2) & 1;
+#pragma unroll
+                    for (int ph = 0; ph < 2; ++ph) {
+                      const int t0 = 8 * (ph ^ sw);  // first token of this physical half
+                      uint32_t x[4];
+                      asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                                   : "=r"(x[0]), "=r"(x[1]), "=r"(x[2]), "=r"(x[3])
+                                   : "r"(row + 16u * ph));
+#pragma unroll
+                      for (int wd = 0; wd < 4; ++wd)
+                        x[wd] &= (t0 + 2 * wd < nv ? 0x0000ffffu : 0u) | (t0 + 2 * wd + 1 < nv ? 0xffff0000u : 0u);
+                      asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(row + 16u * ph), "r"(x[0]), "r"(x[1]),
+                                   "r"(x[2]), "r"(x[3])
+                                   : "memory");
+                    }
+                  }
+                }
+              }
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(v_full + 8 * vs);
+            }
+            if (++vs == kUmmaVStages) {
+              vs = 0;
+              ++vround;
+            }
+          }
+        }
+      }
+    }
   } else if (warp < 12) {
     // ======================= gather warps: pages -> swizzled operand tiles =======================
     // 16 groups of 8 threads: group g serves the 8 keys [8 (g & 7), +8) of the tile; for K it moves half of
@@ -373,12 +480,14 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
     const uint64_t da = sw128_desc(q_s + (uint32_t)w * kUmmaQTile);
     // S_w(step in K ring slot ks) = Q_w K^T into S buffer b, then "S_w[b] ready" and "done with the slot"
     auto issue_qk = [&](int b, int ks) {
-      const uint64_t db = sw128_desc(k_ring + (uint32_t)ks * kUmmaKVTile);
+      const uint32_t k_tile = k_ring + (uint32_t)ks * kUmmaKVTile;
+      // gathered tile: SWIZZLE_128B slabs; TMA tile: [8 keys][chunk][8 keys x 16 B], no swizzle (k-step = 2 chunks)
+      const uint64_t db = TMA ? desc_kmajor(k_tile, 128u, (uint32_t)D * 16u, 0u) : sw128_desc(k_tile);
 #pragma unroll
       for (int kk = 0; kk < D / 16; ++kk) {
         const uint32_t in_slab = (uint32_t)(kk & 3) * 32u;
         mma_ss(t_sw + (uint32_t)b * 64u, desc_advance(da, (uint32_t)(kk >> 2) * 16384u + in_slab),
-               desc_advance(db, (uint32_t)(kk >> 2) * 8192u + in_slab), idesc_s, kk > 0);
+               desc_advance(db, TMA ? (uint32_t)kk * 256u : (uint32_t)(kk >> 2) * 8192u + in_slab), idesc_s, kk > 0);
       }
       commit(s_full + 8 * (2 * w + b));
       commit(k_empty + 8 * ks);
@@ -404,12 +513,14 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p) {
       fence_proxy_async_smem();
       fence_after_sync();
       if (elect_one()) {
-        const uint64_t db = sw128_desc(v_ring + (uint32_t)vs * kUmmaKVTile);
+        const uint32_t v_tile = v_ring + (uint32_t)vs * kUmmaKVTile;
+        // gathered tile: V^T rows of 64 keys, SWIZZLE_128B; TMA tile: one SWIZZLE_32B page (16 keys) per k-step
+        const uint64_t db = TMA ? desc_kmajor(v_tile, 16u, 256u, 6u) : sw128_desc(v_tile);
         const uint32_t t_p = t_sw + (uint32_t)(j & 1) * 64u;
 #pragma unroll
         for (int kk = 0; kk < KT / 16; ++kk)
-          mma_ts(t_ow, t_p + (uint32_t)kk * 8u, desc_advance(db, (uint32_t)kk * 32u), idesc_o,
-                 (j > 0 || kk > 0) ? 1u : 0u);
+          mma_ts(t_ow, t_p + (uint32_t)kk * 8u, desc_advance(db, TMA ? (uint32_t)kk * (uint32_t)(D * BS * 2) : (uint32_t)kk * 32u),
+                 idesc_o, (j > 0 || kk > 0) ? 1u : 0u);
         commit(o_ready + 8 * w);
         commit(v_empty + 8 * vs);
         if (more) issue_qk(j & 1, ks);  // overwrites P_w(j): ordered behind P.V_w(j) in the tensor pipe

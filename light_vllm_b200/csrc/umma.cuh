@@ -29,6 +29,16 @@ __device__ __forceinline__ uint64_t desc_advance(uint64_t desc, uint32_t bytes) 
   return desc + (uint64_t)(bytes >> 4);
 }
 
+// General K-major descriptor: `layout` 0 = no swizzle (core matrix = 8 rows x 16 bytes, contiguous; LBO = byte
+// distance between the two core matrices of one k-step along K, SBO = between 8-row groups along M/N),
+// 6 = SWIZZLE_32B (rows of 32 bytes, 8-row atoms of 256 bytes; SBO between atoms, LBO unused), 2 = SWIZZLE_128B.
+// Checked on a B200 against TMA-written paged tiles by tools/micro/umma_tma_probe.cu.
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t saddr, uint32_t lbo, uint32_t sbo, uint32_t layout) {
+  const uint32_t lo = ((saddr & 0x3FFFFu) >> 4) | ((lbo >> 4) << 16);
+  const uint32_t hi = (sbo >> 4) | (1u << 14) | (layout << 29);
+  return ((uint64_t)hi << 32) | lo;
+}
+
 // Instruction descriptor, kind::f16: D = fp32, A/B = fp16 (fmt 0) or bf16 (fmt 1), both K-major.
 __host__ __device__ constexpr uint32_t idesc_f16(int fmt, int m, int n) {
   return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)(n >> 3) << 17) |
@@ -122,6 +132,21 @@ __device__ __forceinline__ void cp_async_arrive_noinc(uint32_t bar) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// ---- TMA tensor copy (SASS UTMALDG): one box of a 4-D tensor map into shared memory; completion is counted in
+// bytes on the mbarrier (mbarrier.arrive.expect_tx on the consumer's side of the protocol).  `map` points at a
+// CUtensorMap in kernel-parameter (__grid_constant__) or global memory.
+__device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const void* map, int c0, int c1, int c2, int c3,
+                                            uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], "
+      "[%6];" ::"r"(dst_smem),
+      "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
 
 template <int N>
 __device__ __forceinline__ void setmaxnreg_inc() {

@@ -17,6 +17,14 @@ from make_golden_prefix import make_prefix_case  # noqa: E402
 from test_prefix_prefill import TOL, _call, _truth_gpu  # noqa: E402
 
 
+def _same_as_gather(c, got, tol):
+    """BS = 16 calls load K / V tiles with TMA tensor copies; the per-thread 16-byte gather is the other way to fill
+    them (and the only one for other block sizes): same tile loop, same answer."""
+    gat = _run(c, "tcgen05_gather")
+    assert torch.isfinite(gat.float()).all()
+    assert (got.float() - gat.float()).abs().max().item() <= tol
+
+
 def _run(c, path, out=None):
     from light_vllm_b200.attention.prefix_prefill import context_attention_fwd
     d = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in c.items()}
@@ -46,6 +54,7 @@ def test_tcgen05_matches_truth_and_oracle(oracle, dtype, H, KH, BS, D):
     assert (got.float() - ora.float()).abs().max().item() <= TOL[dtype]
     legacy = _run(c, "mma_sync")
     assert (got.float() - legacy.float()).abs().max().item() <= TOL[dtype]
+    _same_as_gather(c, got, TOL[dtype])
 
 
 @pytest.mark.gpu
@@ -71,6 +80,7 @@ def test_tcgen05_nan_poisoned_cache_tails(D):
     got = _run(c, "tcgen05")
     assert torch.isfinite(got.float()).all()
     assert (got.double() - _truth_gpu(c)).abs().max().item() <= 2e-3
+    _same_as_gather(c, got, 2e-3)
 
 
 @pytest.mark.gpu
@@ -90,6 +100,7 @@ def test_tcgen05_fuzz(seed):
     assert torch.isfinite(got.float()).all()
     err = (got.double() - _truth_gpu(c)).abs().max().item()
     assert err <= TOL[dtype], (seed, D, BS, G, KH, dtype, ctx, ql, err)
+    _same_as_gather(c, got, TOL[dtype])
 
 
 @pytest.mark.gpu

@@ -36,7 +36,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--dtype", default="bfloat16")
     ap.add_argument("--no-scratch", action="store_true", help="CTA-local staging of the new k/v")
-    ap.add_argument("--path", default="auto", choices=["auto", "mma_sync", "tcgen05"],
+    ap.add_argument("--path", default="auto", choices=["auto", "mma_sync", "tcgen05", "tcgen05_gather"],
                     help="tile loop: library choice, the mma.sync kernel, or the tcgen05 / TMEM kernel")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
