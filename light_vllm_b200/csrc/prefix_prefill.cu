@@ -680,7 +680,7 @@ int launch_prefix_umma(PrefixParams& p, int num_seqs, int max_query_len, int dev
   if (!configured[slot].load(std::memory_order_acquire)) {
     B200_CUDA_OK(cudaFuncSetAttribute(context_attention_umma_kernel<T, D, BS, false>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUmmaSmem));
-    if constexpr (BS == 16)
+    if constexpr (BS == 16 && D == 128)
       B200_CUDA_OK(cudaFuncSetAttribute(context_attention_umma_kernel<T, D, BS, true>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUmmaSmem));
     configured[slot].store(1, std::memory_order_release);
@@ -692,7 +692,8 @@ int launch_prefix_umma(PrefixParams& p, int num_seqs, int max_query_len, int dev
   dim3 grid(tiles, p.num_kv_heads, num_seqs);
   PrefixTmaMaps maps;
   bool tma = false;
-  if constexpr (BS == 16) {
+  // (head size 64: the boxes shrink to 1-2 KiB and the copies no longer beat the gather -- 538 vs 547 TFLOP/s)
+  if constexpr (BS == 16 && D == 128) {
     auto a16 = [](const void* ptr) { return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0; };
     tma = !gather_only && a16(p.k_cache) && a16(p.v_cache) && p.kc_hs % 8 == 0 && p.kc_bs % 8 == 0 &&
           p.vc_hs % 8 == 0 && p.vc_bs % 8 == 0 &&
@@ -890,3 +891,9 @@ extern "C" int b200_context_attention_fwd(
       vc_head_stride, alibi_slopes, sliding_window, scale, kv_scratch, kv_scratch_bytes, num_tokens, dtype,
       device, stream, B200_PREFIX_PATH_AUTO);
 }
+
+#ifdef B200_UMMA_TRACE
+extern "C" int b200_debug_umma_trace(long long* out) {  // debug build only: [4][128][8] clock64 stamps
+  return (int)cudaMemcpyFromSymbol(out, b200::g_umma_trace, sizeof(long long) * 4 * 128 * 8);
+}
+#endif

@@ -44,6 +44,20 @@
 
 namespace b200 {
 
+#ifdef B200_UMMA_TRACE
+// Debug build only: clock64 stamps of one CTA (blockIdx 0,0,0): [role][step][stamp]; roles 0/1 = softmax warp 0 of
+// M tile 0/1, 2/3 = MMA issuer of M tile 0/1.
+__device__ long long g_umma_trace[4][128][8];
+#define UMMA_STAMP(role, step, i)                                                                    \
+  {                                                                                                  \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (step) < 128)        \
+      g_umma_trace[role][step][i] = clock64();                                                       \
+  }
+#else
+#define UMMA_STAMP(role, step, i) \
+  {}
+#endif
+
 constexpr int kUmmaThreads = 512;
 constexpr int kUmmaRows = 256;          // rows per CTA (two M tiles)
 constexpr int kUmmaKeys = 64;           // keys per step
@@ -166,12 +180,15 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p, const __gr
       float m_ref = kNInf, l = 0.f;
       for (int j = 0; j < nt; ++j) {
         const int b = j & 1;
+        if ((warp & 3) == 0) UMMA_STAMP(w, j, 0)
         mbar_wait_wd(s_full + 8 * (2 * w + b), (uint32_t)((j >> 1) & 1));
         fence_after_sync();
+        if ((warp & 3) == 0) UMMA_STAMP(w, j, 1)
         uint32_t s[2][32];
         tmem_ld32(t_s + 64 * b, s[0]);
         tmem_ld32(t_s + 64 * b + 32, s[1]);
         tmem_wait_ld();
+        if ((warp & 3) == 0) UMMA_STAMP(w, j, 2)
         // visible keys of this row in the tile: a prefix [0, lim)
         int lim;
         if (j < n_ctx_tiles)
@@ -222,6 +239,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p, const __gr
           }
         }
         const float neg_m = m_ref == kNInf ? 0.f : -m_ref;
+        if ((warp & 3) == 0) UMMA_STAMP(w, j, 3)
         float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
         uint32_t pk[32];
 #pragma unroll
@@ -240,10 +258,12 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p, const __gr
             pk[16 * c + i / 2 + 1] = MmaOp<T>::pack(e2, e3);
           }
         }
+        if ((warp & 3) == 0) UMMA_STAMP(w, j, 4)
         tmem_st32(t_s + 64 * b, pk);  // P over the first 32 columns of this S buffer (S is in registers)
         l += (l0 + l1) + (l2 + l3);
         tmem_wait_st();
         fence_before_sync();
+        if ((warp & 3) == 0) UMMA_STAMP(w, j, 5)
         // per S buffer: the softmax may finish step j + 1 before the MMA thread has looked at step j
         mbar_arrive(p_full + 8 * (2 * w + b));
       }
@@ -507,9 +527,13 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p, const __gr
     int vs = 0, vround = 0;
     for (int j = 0; j < nt; ++j) {
       const bool more = j + 2 < nt;
+      UMMA_STAMP(2 + w, j, 0)
       mbar_wait_wd(p_full + 8 * (2 * w + (j & 1)), (uint32_t)((j >> 1) & 1));
+      UMMA_STAMP(2 + w, j, 1)
       mbar_wait_wd(v_full + 8 * vs, (uint32_t)(vround & 1));
+      UMMA_STAMP(2 + w, j, 2)
       if (more) mbar_wait_wd(k_full + 8 * ks, (uint32_t)(kround & 1));
+      UMMA_STAMP(2 + w, j, 3)
       fence_proxy_async_smem();
       fence_after_sync();
       if (elect_one()) {
@@ -526,6 +550,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p, const __gr
         if (more) issue_qk(j & 1, ks);  // overwrites P_w(j): ordered behind P.V_w(j) in the tensor pipe
       }
       __syncwarp();
+      UMMA_STAMP(2 + w, j, 4)
       if (more && ++ks == kUmmaKStages) {
         ks = 0;
         ++kround;
