@@ -907,7 +907,10 @@ def run_b200_arm(args, c):
         torch.cuda.empty_cache()
         for name, fn in (("prefix_prefill", lambda: prefix_prefill_record(dev, args.steps)),
                          ("c3", lambda: other_config_record("c3", dev, args.steps)),
-                         ("c4", lambda: other_config_record("c4", dev, args.steps))):
+                         ("c4", lambda: other_config_record("c4", dev, args.steps)),
+                         # c5's attention launch at full shape (16 x 128 Ki tokens, 16 GiB of K/V in one pool); its
+                         # preemption leg (copy_blocks / swap_blocks) is `--config c5`
+                         ("c5", lambda: other_config_record("c5", dev, max(6, args.steps // 4)))):
             try:
                 extra[name] = fn()
             except Exception as e:  # reported beside the headline, never allowed to take it down
