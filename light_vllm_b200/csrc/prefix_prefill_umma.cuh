@@ -318,12 +318,21 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p, const __gr
           tma_prefetch_desc(maps.k);
           tma_prefetch_desc(maps.v);
         }
-        for (int j = 0; j < nt; ++j) {
+        // (valid keys, block id / staged slice) of this lane's page of tile jj.  The block-table entry of tile j + 1 is
+        // requested while tile j is being issued: one warp runs this loop, and a dependent global load per tile
+        // would sit in a chain that has to stay ahead of the tensor pipe.
+        auto lookup = [&](int jj, int& nv, int& id) {
+          const bool in_ctx = jj < n_ctx_tiles;
+          const int pos = KT * (in_ctx ? jj : jj - n_ctx_tiles) + BS * lane;  // first key of my page
+          nv = (owner && jj < nt) ? min(BS, max(0, (in_ctx ? ctx : qlen) - pos)) : 0;
+          id = 0;
+          if (nv > 0) id = in_ctx ? bt[pos / BS] : slice0 + pos / BS;
+        };
+        int nval, c3, nval_next, c3_next;
+        lookup(0, nval, c3);
+        for (int j = 0; j < nt; ++j, nval = nval_next, c3 = c3_next) {
+          lookup(j + 1, nval_next, c3_next);
           const bool is_ctx = j < n_ctx_tiles;
-          const int pos = KT * (is_ctx ? j : j - n_ctx_tiles) + BS * lane;  // first key of my page
-          const int nval = owner ? min(BS, max(0, (is_ctx ? ctx : qlen) - pos)) : 0;
-          int c3 = 0;
-          if (nval > 0) c3 = is_ctx ? bt[pos / BS] : slice0 + pos / BS;
           const void* kmap = is_ctx ? (const void*)maps.k : (const void*)maps.sk;
           const void* vmap = is_ctx ? (const void*)maps.v : (const void*)maps.sv;
           const uint32_t have = __ballot_sync(FULL, nval > 0);
