@@ -203,6 +203,30 @@ def test_c5_exact(ops, mixed):
     _compare(ops, 2, q, kc, vc, KH, s, bt, lens, BS, ctx, torch.bfloat16)
 
 
+@pytest.mark.parametrize("H,KH,B,ctx,dtype,mixed", [
+    (32, 8, 1, 32768, torch.float16, False),    # v1: cluster 8, no head split, 3 stages; v2: 18 partitions
+    (32, 8, 2, 8192, torch.bfloat16, True),     # v1: cluster 4; v2: 9 partitions
+    (32, 8, 4, 8192, torch.float16, True),      # v1: cluster 4, 2 stages; v2: 4 partitions
+    (32, 8, 8, 4096, torch.bfloat16, False),    # v1: cluster 2; v2: unsplit, 3 stages, no reduce launch
+    (32, 8, 16, 4096, torch.float16, True),     # 128 CTAs, unsplit, 2 stages
+    (28, 4, 4, 8192, torch.bfloat16, True),     # GQA 7 (Qwen2-7B-shaped): 16 CTAs before the split
+    (28, 4, 24, 2048, torch.float16, False),    # 96 CTAs
+])
+def test_one_wave_plans_match_reference(ops, H, KH, B, ctx, dtype, mixed):
+    """Small batches (B * KH <= SMs) run the one-wave plan of make_plan -- one 8-warp CTA per SM, context split only
+    while the grid stays within the SM count, no head split (profiles/r2_small_plan_sweep.md).  Both versions against
+    the reference's CUDA kernels (attention_kernels.cu:690-770, 848-934) on the same scattered pages."""
+    D, BS = 128, 16
+    NB, bt = _tables(B, ctx, BS, 64, seed=40 + B)
+    kc, vc = _pools(NB, KH, D, BS, dtype, seed=41 + B)
+    s = D ** -0.5
+    torch.manual_seed(42 + B)
+    q = torch.empty(B, H, D, dtype=dtype, device="cuda").uniform_(-s, s)
+    lens = _lens(B, ctx, mixed, seed=43 + B)
+    for version in (1, 2):
+        _compare(ops, version, q, kc, vc, KH, s, bt, lens, BS, ctx, dtype)
+
+
 def test_max_grid_batch(ops):
     """num_seqs beyond the 65,535 gridDim.z limit of a naive (split, head, seq) grid: the reference
     puts sequences on gridDim.y (attention_kernels.cu:734) and so accepts B up to 65,535 too; the
