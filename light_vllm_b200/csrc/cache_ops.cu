@@ -63,6 +63,9 @@ reshape_and_cache_kernel(const T* __restrict__ key, const T* __restrict__ value,
                          const int64_t* __restrict__ slot_mapping, int64_t key_stride,
                          int64_t value_stride, int num_heads, int head_size, int block_size, int x,
                          float k_scale, float v_scale) {
+  // The attention launch that follows in a decode step is a programmatic dependent (paged_attention_inst.inc):
+  // let it become resident now and park in griddepcontrol.wait -- it reads nothing before this grid has completed.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int64_t token = blockIdx.x;
   const int64_t slot = slot_mapping[token];
   if (slot < 0) return;  // padding token (cache_kernels.cu:165-169)
@@ -117,6 +120,7 @@ reshape_and_cache_flash_kernel(const T* __restrict__ key, const T* __restrict__ 
                                const int64_t* __restrict__ slot_mapping, int64_t block_stride,
                                int64_t key_stride, int64_t value_stride, int num_heads,
                                int head_size, int block_size, float k_scale, float v_scale) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // see reshape_and_cache_kernel
   const int64_t token = blockIdx.x;
   const int64_t slot = slot_mapping[token];
   if (slot < 0) return;

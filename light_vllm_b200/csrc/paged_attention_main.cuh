@@ -66,6 +66,9 @@ __global__ void __launch_bounds__(B200_ATTN_MAXT, B200_ATTN_MINB) paged_attentio
   // A kernel queued behind this one with programmatic stream serialisation (the context-sharded exchange
   // kernel) may become resident now and park in griddepcontrol.wait; a no-op for ordinary successors.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  // ... and this grid is itself launched as a programmatic dependent (paged_attention_inst.inc): wait for the
+  // predecessor's completion before the first global read (a no-op after an ordinary predecessor).
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   extern __shared__ __align__(128) unsigned char smem[];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
