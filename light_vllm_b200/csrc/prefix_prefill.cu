@@ -462,6 +462,9 @@ __global__ void __launch_bounds__(128) prefix_stage_kv_kernel(const __grid_const
   constexpr int PAGE_BYTES = D * BS * 2;
   constexpr int NDT = D / 8;
   constexpr int VEC_PER_PAGE = BS * NDT;
+  // The tcgen05 tile loop behind this pre-pass is a programmatic dependent: it may start now (Q load, context tiles)
+  // and waits for this grid only before its first read of the staged pages.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   __shared__ __align__(16) unsigned char sm[2 * PAGE_BYTES];
   const int seq = blockIdx.z, kvh = blockIdx.y, sl = blockIdx.x;
   const int qlen = p.seq_lens[seq] - p.ctx_lens[seq];
@@ -698,11 +701,26 @@ int launch_prefix_umma(PrefixParams& p, int num_seqs, int max_query_len, int dev
     tma = !gather_only && a16(p.k_cache) && a16(p.v_cache) && p.kc_hs % 8 == 0 && p.kc_bs % 8 == 0 &&
           p.vc_hs % 8 == 0 && p.vc_bs % 8 == 0 &&
           encode_prefix_maps<D, BS>(p, std::is_same<T, __nv_bfloat16>::value, maps);
-    if (tma) context_attention_umma_kernel<T, D, BS, true><<<grid, kUmmaThreads, kUmmaSmem, stream>>>(p, maps);
+  }
+  // Programmatic dependent of the staging pre-pass launched above (same stream): the kernel executes
+  // griddepcontrol.wait right before its first read of the staged pages and nowhere else -- everything it touches
+  // earlier (q, block tables, the cache) was complete before the pre-pass itself could start.
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(kUmmaThreads);
+  cfg.dynamicSmemBytes = kUmmaSmem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if constexpr (BS == 16 && D == 128) {
+    if (tma) B200_CUDA_OK(cudaLaunchKernelEx(&cfg, context_attention_umma_kernel<T, D, BS, true>, p, maps));
   }
   if (!tma) {
     memset(&maps, 0, sizeof(maps));
-    context_attention_umma_kernel<T, D, BS, false><<<grid, kUmmaThreads, kUmmaSmem, stream>>>(p, maps);
+    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, context_attention_umma_kernel<T, D, BS, false>, p, maps));
   }
   count_launch();
   B200_CUDA_OK(cudaGetLastError());

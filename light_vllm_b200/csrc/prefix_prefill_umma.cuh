@@ -333,6 +333,9 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p, const __gr
         for (int j = 0; j < nt; ++j, nval = nval_next, c3 = c3_next) {
           lookup(j + 1, nval_next, c3_next);
           const bool is_ctx = j < n_ctx_tiles;
+          // first tile of new tokens: the staging pre-pass (prefix_stage_kv_kernel, this grid's programmatic
+          // predecessor) must have completed before its pages are fetched
+          if (j == n_ctx_tiles) asm volatile("griddepcontrol.wait;" ::: "memory");
           const void* kmap = is_ctx ? (const void*)maps.k : (const void*)maps.sk;
           const void* vmap = is_ctx ? (const void*)maps.v : (const void*)maps.sv;
           const uint32_t have = __ballot_sync(FULL, nval > 0);
@@ -426,6 +429,7 @@ context_attention_umma_kernel(const __grid_constant__ PrefixParams p, const __gr
     int ks = 0, kround = 0, vs = 0, vround = 0;  // ring positions of tile j, times each ring wrapped
     for (int j = 0; j < nt; ++j) {
       const bool is_ctx = j < n_ctx_tiles;
+      if (j == n_ctx_tiles) asm volatile("griddepcontrol.wait;" ::: "memory");  // staged pages: see the TMA producer
       const int pos = KT * (is_ctx ? j : j - n_ctx_tiles) + 8 * kg;  // first key of the group
       const int nval = min(8, max(0, (is_ctx ? ctx : qlen) - pos));  // its valid keys
       const int toff = pos % BS;
