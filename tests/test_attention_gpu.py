@@ -377,3 +377,56 @@ def test_writes_only_its_output_rows(ops, version, H, KH, D, BS):
     live = torch.tensor(lens) > 0
     want = naive_attention(c)
     assert (out.double().cpu()[live] - want[live]).abs().max().item() <= 2e-3
+
+
+@pytest.mark.parametrize("version", [1, 2])
+def test_graph_capture_behind_copy_and_cache_write(ops, version):
+    """The attention kernels are launched as programmatic dependents (griddepcontrol.wait at entry) and
+    reshape_and_cache releases its dependents at entry.  Captured in a CUDA graph behind (a) a host-to-device copy
+    node and (b) the cache write of the newest token, the replay must equal the same sequence run eagerly -- with
+    the query and the new token changed between capture and replay."""
+    lens = [1, 100, 513, 1024, 2047]
+    B, H, KH, D, BS = len(lens), 32, 8, 128, 16
+    c = to_device(make_case(B, H, KH, D, BS, lens, torch.float16, seed=21), "cuda")
+    g = torch.Generator().manual_seed(5)
+    s = c["scale"]
+    q_host = [((torch.rand(B, H, D, generator=g) * 2 - 1) * s).half().pin_memory() for _ in range(2)]
+    kv_host = [((torch.rand(2, B, KH, D, generator=g) * 2 - 1) * s).half().pin_memory() for _ in range(2)]
+    slots = torch.tensor([int(c["block_tables"][i, (n - 1) // BS]) * BS + (n - 1) % BS for i, n in enumerate(lens)],
+                         dtype=torch.int64, device="cuda")
+    q_dev = torch.empty(B, H, D, dtype=torch.float16, device="cuda")
+    kv_dev = torch.empty(2, B, KH, D, dtype=torch.float16, device="cuda")
+    out = torch.empty_like(q_dev)
+    es, ml, tmp = v2_scratch(c, device="cuda")
+
+    def step(qh, kvh):
+        q_dev.copy_(qh, non_blocking=True)      # memcpy node in front of the first kernel
+        kv_dev.copy_(kvh, non_blocking=True)
+        ops.reshape_and_cache(kv_dev[0], kv_dev[1], c["key_cache"], c["value_cache"], slots, "auto", 1.0, 1.0)
+        args = (q_dev, c["key_cache"], c["value_cache"], KH, s, c["block_tables"], c["seq_lens"], BS,
+                c["max_seq_len"], None, "auto", 1.0, 1.0, *TAIL)
+        if version == 1:
+            ops.paged_attention_v1(out, *args)
+        else:
+            ops.paged_attention_v2(out, es, ml, tmp, *args)
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        step(q_host[0], kv_host[0])
+        side.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            step(q_host[0], kv_host[0])
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    # replay on other data (the graph reads the same pinned buffers: overwrite them in place)
+    q_host[0].copy_(q_host[1])
+    kv_host[0].copy_(kv_host[1])
+    graph.replay()
+    torch.cuda.synchronize()
+    got = out.clone()
+    step(q_host[1], kv_host[1])
+    torch.cuda.synchronize()
+    assert not torch.isnan(got.float()).any()
+    assert torch.equal(got, out)
