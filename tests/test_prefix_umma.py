@@ -152,3 +152,37 @@ def test_tcgen05_prefill_heavy_shape():
     c = make_prefix_case([4096] * 4, [512] * 4, 32, 8, 128, 16, torch.bfloat16, seed=11)
     got = _run(c, "tcgen05")
     assert (got.double() - _truth_gpu(c)).abs().max().item() <= 1e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", ["tcgen05", "tcgen05_gather"])
+def test_tcgen05_graph_capture(path):
+    """Staging pre-pass + tile loop (its programmatic dependent; the TMA variant carries four tensor maps as kernel
+    parameters) captured in a CUDA graph and replayed on other queries / new tokens: equal to the eager call."""
+    from light_vllm_b200.attention.prefix_prefill import context_attention_fwd
+    c = make_prefix_case([700, 48, 256, 0], [130, 64, 257, 40], 8, 2, 128, 16, torch.bfloat16, seed=4)
+    d = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in c.items()}
+    fn = functools.partial(context_attention_fwd, path=path)
+    out = torch.zeros_like(d["query"])
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        _call(fn, d, out)
+        side.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            _call(fn, d, out)
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.Generator(device="cuda").manual_seed(9)
+    for name in ("query", "key", "value"):
+        d[name].copy_((torch.rand(d[name].shape, generator=g, device="cuda") * 2 - 1).to(d[name].dtype) * 0.09)
+    out.fill_(float("nan"))
+    graph.replay()
+    torch.cuda.synchronize()
+    got = out.clone()
+    want = _call(fn, d, torch.zeros_like(out))
+    torch.cuda.synchronize()
+    assert torch.isfinite(got.float()).all()
+    assert torch.equal(got, want)
+    assert (got.double().cpu() - _truth_gpu({k: (v.cpu() if isinstance(v, torch.Tensor) else v) for k, v in d.items()})).abs().max().item() <= TOL[torch.bfloat16]
