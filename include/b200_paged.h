@@ -19,6 +19,12 @@
  *     int, attention_kernels.cu:705-707; pools above 2^31 elements need 64 bits).
  *   - there is no CPU implementation behind any of these symbols: without a CUDA device they
  *     fail with B200_ERR_CUDA.
+ *   - launch ordering: every call is ordered behind the work already queued on `stream`, as the
+ *     reference's launches are.  The attention kernels are launched with programmatic stream
+ *     serialization and start with griddepcontrol.wait: when the preceding kernel on the stream is
+ *     b200_reshape_and_cache[_flash] (or another kernel that executes griddepcontrol.launch_dependents)
+ *     their launch latency overlaps it, behind anything else they are ordinary launches.  Nothing is
+ *     required of the caller, and the calls can be captured in CUDA graphs.
  */
 #ifndef B200_PAGED_H_
 #define B200_PAGED_H_
