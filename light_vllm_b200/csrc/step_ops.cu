@@ -121,6 +121,9 @@ rotary_reshape_and_cache_kernel(const int64_t* __restrict__ positions, T* __rest
                                 int64_t query_stride, int64_t key_stride, int64_t value_stride,
                                 int num_heads, int num_kv_heads, int head_size, int block_size,
                                 int x, float k_scale, float v_scale) {
+  // like reshape_and_cache: the attention launch behind this kernel is a programmatic dependent that reads nothing
+  // (query, cache) before this grid has completed -- let it become resident now
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int64_t token = blockIdx.x;
   const int64_t pos = positions[token] + (offsets ? offsets[token] : 0);
   const T* cache_ptr = cos_sin_cache + pos * rot_dim;
