@@ -240,7 +240,8 @@ def ncu_traffic(config_name):
 
 
 class ClockSampler:
-    """SM clock and throttle reasons sampled DURING the timed region (NVML every ~2 ms in a thread;
+    """SM clock and throttle reasons sampled DURING the timed region (NVML every ~0.5 ms in a thread -- the
+    default timed region lasts only ~7 ms;
     falls back to `nvidia-smi -lms` when the NVML binding is unavailable)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -275,7 +276,7 @@ class ClockSampler:
                                 self.reasons.add(n)
                     except Exception:
                         pass
-                    time.sleep(0.002)
+                    time.sleep(0.0005)
 
             self.thread = threading.Thread(target=poll, daemon=True)
             self.thread.start()
